@@ -1,0 +1,183 @@
+"""ctypes bindings for the CPU checker (oracle/liboracle.so) and, when present, the compiled reference
+(oracle/_ref/libref_*.so). TEST INFRASTRUCTURE: imported only by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs. Never by the product package."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_DIR = os.path.join(ORACLE_DIR, "_ref")
+REFERENCE_SRC = "/root/reference"
+
+MAX_JOBS = 20
+NODE_I16 = 2 + MAX_JOBS
+MAX_QUEENS = 20
+NQ_REC = 1 + MAX_QUEENS
+
+i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+i16p = np.ctypeslib.ndpointer(dtype=np.int16, flags="C_CONTIGUOUS")
+u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+ullp = C.POINTER(C.c_ulonglong)
+
+
+class RunStats(C.Structure):
+    _fields_ = [("tree", C.c_ulonglong), ("sol", C.c_ulonglong), ("parents", C.c_ulonglong),
+                ("evals", C.c_ulonglong), ("depth_hist", C.c_ulonglong * 64), ("best", C.c_int),
+                ("max_pool", C.c_int)]
+
+
+def build_oracle(ref=False):
+    """(re)build liboracle.so; with ref=True also oracle/_ref when the reference sources are present."""
+    subprocess.run(["make", "-C", ORACLE_DIR, "-s"], check=True)
+    if ref and os.path.isdir(REFERENCE_SRC):
+        subprocess.run(["make", "-C", ORACLE_DIR, "-s", "ref"], check=True, stderr=subprocess.DEVNULL)
+
+
+_oracle = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is not None:
+        return _oracle
+    path = os.path.join(ORACLE_DIR, "liboracle.so")
+    if not os.path.exists(path):
+        build_oracle()
+    L = C.CDLL(path)
+    L.orc_pfsp_new.restype = C.c_void_p
+    L.orc_pfsp_new.argtypes = [C.c_int]
+    L.orc_pfsp_from_ptimes.restype = C.c_void_p
+    L.orc_pfsp_from_ptimes.argtypes = [C.c_int, C.c_int, i32p]
+    L.orc_pfsp_free.argtypes = [C.c_void_p]
+    L.orc_pfsp_tables.argtypes = [C.c_void_p] + [i32p] * 8
+    L.orc_taillard_ptimes.argtypes = [C.c_int, i32p]
+    L.orc_taillard_seed.restype = C.c_long
+    L.orc_fnv1a_i32.restype = C.c_uint64
+    L.orc_fnv1a_i32.argtypes = [i32p, C.c_int]
+    L.orc_makespan.argtypes = [C.c_void_p, i32p]
+    L.orc_lb1.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int]
+    L.orc_lb1_children.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, i32p]
+    L.orc_lb2.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_int]
+    L.orc_lb2_census.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_int, ullp, ullp]
+    L.orc_batch_index.argtypes = [i16p, C.c_int, C.c_int, i32p, i32p]
+    L.orc_evaluate_chunk.argtypes = [C.c_void_p, C.c_int, i16p, C.c_int, C.c_int, i32p]
+    L.orc_generate_children.argtypes = [i16p, C.c_int, C.c_int, i32p, ullp, ullp, C.POINTER(C.c_int), i16p]
+    L.orc_pfsp_search.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.POINTER(RunStats)]
+    L.orc_pfsp_search_batched.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(RunStats), ullp]
+    L.orc_nq_is_safe.argtypes = [C.c_int, u8p, C.c_int, C.c_int]
+    L.orc_nq_labels.argtypes = [C.c_int, C.c_int, u8p, C.c_int, u8p]
+    L.orc_nq_generate_children.argtypes = [C.c_int, u8p, C.c_int, u8p, ullp, ullp, u8p]
+    L.orc_nq_search.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(RunStats)]
+    _oracle = L
+    return L
+
+
+def have_ref():
+    return os.path.exists(os.path.join(REF_DIR, "libref_pfsp.so"))
+
+
+_ref_pfsp = None
+_ref_nq = None
+
+
+def ref_pfsp():
+    global _ref_pfsp
+    if _ref_pfsp is None:
+        L = C.CDLL(os.path.join(REF_DIR, "libref_pfsp.so"))
+        L.ref_pfsp_open.restype = C.c_void_p
+        L.ref_pfsp_open.argtypes = [C.c_int]
+        L.ref_pfsp_close.argtypes = [C.c_void_p]
+        L.ref_pfsp_dims.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4
+        L.ref_pfsp_tables.argtypes = [C.c_void_p] + [i32p] * 8
+        L.ref_lb1_bound.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int]
+        L.ref_lb1_children_bounds.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, i32p]
+        L.ref_lb2_bound.argtypes = [C.c_void_p, i32p, C.c_int, C.c_int, C.c_int]
+        L.ref_eval_solution.argtypes = [C.c_void_p, i32p]
+        L.ref_pfsp_search.restype = C.c_ulonglong
+        L.ref_pfsp_search.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), ullp, ullp, C.c_longlong]
+        L.ref_pfsp_decompose.argtypes = [C.c_void_p, C.c_int, i16p, C.c_int, C.POINTER(C.c_int), ullp, ullp, i16p]
+        L.ref_generate_children.argtypes = [i16p, C.c_int, C.c_int, i32p, ullp, ullp, C.POINTER(C.c_int), i16p]
+        _ref_pfsp = L
+    return _ref_pfsp
+
+
+def ref_nq():
+    global _ref_nq
+    if _ref_nq is None:
+        L = C.CDLL(os.path.join(REF_DIR, "libref_nqueens.so"))
+        L.ref_nq_is_safe.argtypes = [C.c_int, u8p, C.c_int, C.c_int]
+        L.ref_nq_decompose.argtypes = [C.c_int, C.c_int, u8p, C.c_int, ullp, ullp, u8p]
+        L.ref_nq_search.restype = C.c_ulonglong
+        L.ref_nq_search.argtypes = [C.c_int, C.c_int, ullp, ullp, C.c_longlong]
+        _ref_nq = L
+    return _ref_nq
+
+
+class Tables:
+    """numpy view of one instance's precomputed tables from either implementation."""
+
+    def __init__(self, n, m, P):
+        self.n, self.m, self.P = n, m, P
+        z = lambda k: np.zeros(max(k, 1), dtype=np.int32)
+        self.p, self.heads, self.tails = z(n * m), z(m), z(m)
+        self.lags, self.johnson = z(P * n), z(P * n)
+        self.pa, self.pb, self.order = z(P), z(P), z(P)
+
+    def arrays(self):
+        return [self.p, self.heads, self.tails, self.lags, self.johnson, self.pa, self.pb, self.order]
+
+
+def taillard_dims(inst):
+    L = oracle()
+    return L.orc_taillard_jobs(inst), L.orc_taillard_machines(inst)
+
+
+def oracle_tables(inst):
+    L = oracle()
+    n, m = taillard_dims(inst)
+    h = L.orc_pfsp_new(inst)
+    t = Tables(n, m, m * (m - 1) // 2)
+    L.orc_pfsp_tables(h, *t.arrays())
+    L.orc_pfsp_free(h)
+    return t
+
+
+def ref_tables(inst):
+    R = ref_pfsp()
+    h = R.ref_pfsp_open(inst)
+    n, m, P, ub = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    R.ref_pfsp_dims(h, n, m, P, ub)
+    t = Tables(n.value, m.value, P.value)
+    R.ref_pfsp_tables(h, *t.arrays())
+    R.ref_pfsp_close(h)
+    t.best_ub = ub.value
+    return t
+
+
+def fnv(a):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    return int(oracle().orc_fnv1a_i32(a, a.size))
+
+
+def random_pfsp_nodes(rng, n, count, min_depth=0, max_depth=None):
+    """random partial permutations as flat reference Node records [depth, limit1, prmu[20]]"""
+    max_depth = n - 1 if max_depth is None else max_depth
+    out = np.zeros((count, NODE_I16), dtype=np.int16)
+    for i in range(count):
+        d = int(rng.integers(min_depth, max_depth + 1))
+        out[i, 0] = d
+        out[i, 1] = d - 1
+        out[i, 2:2 + n] = rng.permutation(n)
+    return out
+
+
+def random_nq_nodes(rng, N, count, min_depth=0, max_depth=None):
+    max_depth = N if max_depth is None else max_depth
+    out = np.zeros((count, NQ_REC), dtype=np.uint8)
+    for i in range(count):
+        out[i, 0] = int(rng.integers(min_depth, max_depth + 1))
+        out[i, 1:1 + N] = rng.permutation(N)
+    return out
