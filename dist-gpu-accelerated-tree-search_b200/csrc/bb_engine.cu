@@ -1,0 +1,778 @@
+/*
+ * bb_engine.cu - host side of the native engine: device pool, table upload, CUDA-graph iteration chains,
+ * seeding / export in the reference's node layouts, statistics. C ABI declared in include/bb_gpu.h.
+ *
+ * What of the reference this replaces (all host code there):
+ *   SinglePool_atom push/pop/realloc              pfsp/lib/Pool_atom.c:4-258        -> two device stacks + bb_ctrl
+ *   lb1_alloc_gpu / lb2_alloc_gpu table upload    pfsp/lib/PFSP_gpu_lib.cu:154-200  -> upload_pfsp_tables (repacked)
+ *   the while(1) batch loop                       pfsp/pfsp_multigpu_cuda.c:221-320 -> bb_engine_run (graph chains)
+ *   CPU warm-up and drain (steps 1 and 3)         pfsp_multigpu_cuda.c:111-118, 487-495 -> same device loop
+ */
+#include "bb_internal.cuh"
+#include "bb_nq_kernels.cuh"
+#include "bb_pfsp_kernels.cuh"
+
+#include <climits>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+/* ------------------------------------------------------------------ errors */
+
+static thread_local char g_err[512] = "";
+static thread_local int g_cuda_err = 0;
+
+extern "C" const char *bb_last_error(void) { return g_err; }
+extern "C" int bb_last_cuda_error(void) { return g_cuda_err; }
+
+int bb_fail(int code, const char *fmt, ...)
+{
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int bb_fail_cuda(cudaError_t err, const char *what, const char *file, int line)
+{
+  g_cuda_err = (int)err;
+  snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s:%d: %s", (int)err, cudaGetErrorString(err), file, line,
+           what);
+  return BB_ERR_CUDA;
+}
+
+void bb_note_cuda(cudaError_t err, const char *what)
+{
+  if (err != cudaSuccess)
+  {
+    g_cuda_err = (int)err;
+    snprintf(g_err, sizeof(g_err), "CUDA error %d (%s): %s", (int)err, cudaGetErrorString(err), what);
+  }
+}
+
+/* ------------------------------------------------------------------ engine object */
+
+enum
+{
+  KIND_PFSP = 1,
+  KIND_NQ = 2
+};
+
+struct bb_engine
+{
+  int kind;
+  int device;
+  cudaStream_t stream;
+  bb_ctrl *ctrl;   /* device */
+  bb_ctrl *ctrl_h; /* pinned host mirror */
+  bb_pool pool;
+  void *pool_mem[2];
+  void *tail_mem[2];
+  /* PFSP */
+  bb_pfsp_dev T;
+  void *table_mem;
+  int lb, n, m, prefilter;
+  /* N-Queens */
+  int N, G;
+  /* launch */
+  const void *kernel;
+  int grid, smem;
+  int iters_per_launch;
+  cudaGraphExec_t graph;
+  cudaEvent_t ev0, ev1;
+  double kernel_ms;
+  unsigned long long launches;
+  int M, m_keep;
+};
+
+#define ENGINE_SET_DEVICE(e) BB_CUDA_TRY(cudaSetDevice((e)->device))
+
+extern "C" void bb_config_default(bb_config *cfg)
+{
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->device = 0;
+  cfg->M = 50000; /* PFSP_lib.c:179 */
+  cfg->m = 25;    /* PFSP_lib.c:178 */
+  cfg->capacity = 0;
+  cfg->iters_per_launch = 32;
+  cfg->lb2_prefilter = 1;
+}
+
+/* ------------------------------------------------------------------ small kernels: plan / seed / export */
+
+__global__ void k_plan(bb_ctrl *c, int add0, int total_warps)
+{
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+  {
+    c->size[0] += add0;
+    bbk::plan_next(c, 0, total_warps);
+  }
+}
+
+__global__ void k_reset(bb_ctrl *c, int best, int M, int capacity, int maxkids)
+{
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+  {
+    int *raw = reinterpret_cast<int *>(c);
+    for (unsigned i = 0; i < sizeof(bb_ctrl) / sizeof(int); i++)
+      raw[i] = 0;
+    c->best = best;
+    c->M = M;
+    c->capacity = capacity;
+    c->maxkids = maxkids;
+    c->tile = 1;
+  }
+}
+
+__global__ void k_set_best(bb_ctrl *c, int best) { atomicMin(&c->best, best); }
+
+/* reference Node (int16 depth, limit1, prmu[20]) -> device record, deriving front/remain/mask
+ * (schedule_front + sum_unscheduled of c_bound_simple.c:51-68, 108-124, done once per seeded node only) */
+__global__ void k_seed_pfsp(const int16_t *__restrict__ nodes, int count, bb_pool pool, bb_pfsp_dev T, int at,
+                            int mp, int nplanes)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const int16_t *nd = nodes + (size_t)i * (2 + BB_MAX_JOBS);
+  const int depth = nd[0];
+  uint32_t w[28];
+  for (int q = 0; q < 28; q++)
+    w[q] = 0;
+  uint32_t mask = 0;
+  for (int j = 0; j < T.n; j++)
+  {
+    const uint32_t job = (uint32_t)nd[2 + j] & 0xffu;
+    w[j >> 2] |= job << (8 * (j & 3));
+    if (j < depth)
+      mask |= 1u << job;
+  }
+  w[5] = (uint32_t)depth | (mask << 8);
+  int front[BB_MAX_MACHINES], remain[BB_MAX_MACHINES];
+  for (int k = 0; k < T.m; k++)
+  {
+    front[k] = 0;
+    remain[k] = 0;
+  }
+  for (int j = 0; j < T.n; j++)
+  {
+    const int job = nd[2 + j];
+    if (j < depth)
+    {
+      front[0] += T.p8[job];
+      for (int k = 1; k < T.m; k++)
+        front[k] = max(front[k - 1], front[k]) + T.p8[k * BB_MAX_JOBS + job];
+    }
+    else
+      for (int k = 0; k < T.m; k++)
+        remain[k] += T.p8[k * BB_MAX_JOBS + job];
+  }
+  uint16_t *h = reinterpret_cast<uint16_t *>(w);
+  for (int k = 0; k < T.m; k++)
+  {
+    h[12 + k] = (uint16_t)front[k];
+    h[12 + mp + k] = (uint16_t)remain[k];
+  }
+  for (int q = 0; q < nplanes; q++)
+    pool.planes[0][(size_t)q * pool.capacity + at + i] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+}
+
+__global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int stack, int count, int out_at)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const uint4 q0 = pool.planes[stack][i];
+  const uint4 q1 = pool.planes[stack][(size_t)pool.capacity + i];
+  const uint32_t w[6] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y};
+  int16_t *nd = nodes + (size_t)(out_at + i) * (2 + BB_MAX_JOBS);
+  const int depth = w[5] & 0xff;
+  nd[0] = (int16_t)depth;
+  nd[1] = (int16_t)(depth - 1);
+  for (int j = 0; j < BB_MAX_JOBS; j++)
+    nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
+}
+
+/* reference N-Queens Node (uint8 depth, board[20]) <-> device record */
+__global__ void k_seed_nq(const uint8_t *__restrict__ nodes, int count, bb_pool pool, int N, int at)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const uint8_t *nd = nodes + (size_t)i * (1 + BB_MAX_QUEENS);
+  unsigned char rec[24];
+  for (int b = 0; b < 24; b++)
+    rec[b] = 0;
+  for (int j = 0; j < N; j++)
+    rec[j] = nd[1 + j];
+  rec[N <= 15 ? 15 : N] = nd[0];
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(rec);
+  uint32_t ww[6];
+  for (int q = 0; q < 6; q++)
+    ww[q] = (uint32_t)rec[4 * q] | ((uint32_t)rec[4 * q + 1] << 8) | ((uint32_t)rec[4 * q + 2] << 16) |
+            ((uint32_t)rec[4 * q + 3] << 24);
+  (void)w;
+  pool.planes[0][at + i] = make_uint4(ww[0], ww[1], ww[2], ww[3]);
+  for (int t = 0; t < pool.tail_words; t++)
+    pool.tailw[0][(size_t)(at + i) * pool.tail_words + t] = ww[4 + t];
+}
+
+__global__ void k_export_nq(uint8_t *__restrict__ nodes, bb_pool pool, int stack, int count, int out_at, int N)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const uint4 q0 = pool.planes[stack][i];
+  uint32_t ww[6] = {q0.x, q0.y, q0.z, q0.w, 0u, 0u};
+  for (int t = 0; t < pool.tail_words; t++)
+    ww[4 + t] = pool.tailw[stack][(size_t)i * pool.tail_words + t];
+  uint8_t *nd = nodes + (size_t)(out_at + i) * (1 + BB_MAX_QUEENS);
+  const int db = N <= 15 ? 15 : N;
+  nd[0] = (uint8_t)((ww[db >> 2] >> (8 * (db & 3))) & 0xff);
+  for (int j = 0; j < BB_MAX_QUEENS; j++)
+    nd[1 + j] = j < N ? (uint8_t)((ww[j >> 2] >> (8 * (j & 3))) & 0xff) : 0;
+}
+
+/* ------------------------------------------------------------------ creation */
+
+static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tail_words)
+{
+  bb_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    bb_config_default(&c);
+  e->device = c.device;
+  e->M = c.M > 0 ? c.M : 50000;
+  e->m_keep = c.m > 0 ? c.m : 25;
+  e->iters_per_launch = c.iters_per_launch > 0 ? c.iters_per_launch : 32;
+  ENGINE_SET_DEVICE(e);
+  long long capacity = c.capacity;
+  if (capacity <= 0)
+  {
+    /* depth-first batches of M leave up to M*(branching-1) nodes behind per level: size for that, within a
+     * third of the free HBM (a B200 has 180 GB; the pool is the only large allocation of the engine) */
+    size_t free_b = 0, total_b = 0;
+    BB_CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
+    const long long rec = (long long)nplanes * 16 + (long long)tail_words * 4;
+    const long long by_mem = (long long)(free_b / 3) / (2 * rec);
+    capacity = (long long)e->M * 256;
+    if (capacity < (1 << 22))
+      capacity = 1 << 22;
+    if (capacity > by_mem)
+      capacity = by_mem;
+  }
+  if (capacity > (1ll << 30))
+    capacity = 1ll << 30;
+  if (capacity < 1024)
+    return bb_fail(BB_ERR_ARG, "pool capacity %lld is too small", capacity);
+  ENGINE_SET_DEVICE(e);
+  BB_CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  BB_CUDA_TRY(cudaEventCreate(&e->ev0));
+  BB_CUDA_TRY(cudaEventCreate(&e->ev1));
+  BB_CUDA_TRY(cudaMalloc(&e->ctrl, sizeof(bb_ctrl)));
+  BB_CUDA_TRY(cudaMallocHost(&e->ctrl_h, sizeof(bb_ctrl)));
+  e->pool.capacity = (int)capacity;
+  e->pool.nplanes = nplanes;
+  e->pool.tail_words = tail_words;
+  for (int s = 0; s < 2; s++)
+  {
+    BB_CUDA_TRY(cudaMalloc(&e->pool_mem[s], (size_t)capacity * nplanes * sizeof(uint4)));
+    e->pool.planes[s] = (uint4 *)e->pool_mem[s];
+    e->pool.tailw[s] = nullptr;
+    if (tail_words)
+    {
+      BB_CUDA_TRY(cudaMalloc(&e->tail_mem[s], (size_t)capacity * tail_words * sizeof(uint32_t)));
+      e->pool.tailw[s] = (uint32_t *)e->tail_mem[s];
+    }
+  }
+  return BB_OK;
+}
+
+static int setup_launch(bb_engine *e, const void *kernel, int smem)
+{
+  e->kernel = kernel;
+  e->smem = smem;
+  if (smem > 48 * 1024)
+    BB_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  int per_sm = 0, sms = 0;
+  BB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BB_CTA_THREADS, smem));
+  BB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device));
+  if (per_sm < 1)
+    return bb_fail(BB_ERR_CUDA, "kernel does not fit on an SM (smem %d B)", smem);
+  e->grid = per_sm * sms; /* persistent-style: every CTA resident, a multiple of the SM count */
+  return BB_OK;
+}
+
+static int launch_expand(bb_engine *e, cudaStream_t s)
+{
+  if (e->kind == KIND_PFSP)
+  {
+    void *args[] = {&e->ctrl, &e->pool, &e->T, &e->prefilter};
+    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(BB_CTA_THREADS), args, e->smem, s));
+  }
+  else
+  {
+    void *args[] = {&e->ctrl, &e->pool, &e->N, &e->G};
+    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(BB_CTA_THREADS), args, e->smem, s));
+  }
+  return BB_OK;
+}
+
+static int build_graph(bb_engine *e)
+{
+  cudaGraph_t g;
+  BB_CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+  for (int i = 0; i < e->iters_per_launch; i++)
+  {
+    int rc = launch_expand(e, e->stream);
+    if (rc)
+    {
+      cudaStreamEndCapture(e->stream, &g);
+      return rc;
+    }
+  }
+  BB_CUDA_TRY(cudaStreamEndCapture(e->stream, &g));
+  BB_CUDA_TRY(cudaGraphInstantiate(&e->graph, g, 0));
+  BB_CUDA_TRY(cudaGraphDestroy(g));
+  return BB_OK;
+}
+
+template <int LB>
+static const void *pick_pfsp_kernel(int mm)
+{
+  switch (mm)
+  {
+  case 5:
+    return (const void *)bbk::pfsp_expand<LB, 5>;
+  case 10:
+    return (const void *)bbk::pfsp_expand<LB, 10>;
+  case 20:
+    return (const void *)bbk::pfsp_expand<LB, 20>;
+  default:
+    return (const void *)bbk::pfsp_expand<LB, 0>;
+  }
+}
+
+static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
+{
+  const int n = ins->nb_jobs, m = ins->nb_machines, P = ins->nb_machine_pairs;
+  const size_t sz_p8 = ((size_t)m * BB_MAX_JOBS + 15) & ~(size_t)15;
+  const size_t sz_vec = ((size_t)m * 4 + 15) & ~(size_t)15;
+  const size_t sz_slot = ((size_t)(P > 0 ? P : 1) * BB_MAX_JOBS * 4 + 15) & ~(size_t)15;
+  const size_t sz_pairs = ((size_t)(P > 0 ? P : 1) * 8 + 15) & ~(size_t)15;
+  const size_t total = sz_p8 + 2 * sz_vec + 3 * sz_slot + sz_pairs;
+  std::vector<unsigned char> h(total, 0);
+  uint8_t *p8 = h.data();
+  int *tails = (int *)(h.data() + sz_p8);
+  int *heads = (int *)(h.data() + sz_p8 + sz_vec);
+  uint32_t *jbit = (uint32_t *)(h.data() + sz_p8 + 2 * sz_vec);
+  int *ja = (int *)(h.data() + sz_p8 + 2 * sz_vec + sz_slot);
+  int *jb = (int *)(h.data() + sz_p8 + 2 * sz_vec + 2 * sz_slot);
+  int2 *pairs = (int2 *)(h.data() + sz_p8 + 2 * sz_vec + 3 * sz_slot);
+  for (int k = 0; k < m; k++)
+  {
+    for (int j = 0; j < n; j++)
+    {
+      const int v = ins->p_times[k * n + j];
+      if (v < 0 || v > 255)
+        return bb_fail(BB_ERR_ARG, "processing time %d out of the supported 0..255 range", v);
+      p8[k * BB_MAX_JOBS + j] = (uint8_t)v;
+    }
+    tails[k] = ins->min_tails[k];
+    heads[k] = ins->min_heads[k];
+  }
+  for (int l = 0; l < P; l++)
+  {
+    const int s = ins->machine_pair_order[l];
+    const int m1 = ins->machine_pairs_1[s], m2 = ins->machine_pairs_2[s];
+    pairs[l] = make_int2(m1, m2);
+    for (int q = 0; q < n; q++)
+    {
+      const int job = ins->johnson_schedules[s * n + q];
+      jbit[l * BB_MAX_JOBS + q] = 1u << job;
+      ja[l * BB_MAX_JOBS + q] = ins->p_times[m2 * n + job] - ins->p_times[m1 * n + job];
+      jb[l * BB_MAX_JOBS + q] = ins->lags[s * n + job] + ins->p_times[m2 * n + job];
+    }
+  }
+  BB_CUDA_TRY(cudaMalloc(&e->table_mem, total));
+  BB_CUDA_TRY(cudaMemcpy(e->table_mem, h.data(), total, cudaMemcpyHostToDevice));
+  unsigned char *d = (unsigned char *)e->table_mem;
+  e->T.n = n;
+  e->T.m = m;
+  e->T.mp = bbk::pfsp_mp(m);
+  e->T.P = P;
+  e->T.p8 = d;
+  e->T.tails = (const int *)(d + sz_p8);
+  e->T.heads = (const int *)(d + sz_p8 + sz_vec);
+  e->T.jbit = (const uint32_t *)(d + sz_p8 + 2 * sz_vec);
+  e->T.ja = (const int *)(d + sz_p8 + 2 * sz_vec + sz_slot);
+  e->T.jb = (const int *)(d + sz_p8 + 2 * sz_vec + 2 * sz_slot);
+  e->T.pairs = (const int2 *)(d + sz_p8 + 2 * sz_vec + 3 * sz_slot);
+  e->T.best_known = ins->best_known;
+  return BB_OK;
+}
+
+static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
+{
+  e->kind = KIND_PFSP;
+  e->lb = lb;
+  e->n = ins->nb_jobs;
+  e->m = ins->nb_machines;
+  e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
+  int rc = alloc_common(e, cfg, bbk::pfsp_planes(e->m), 0);
+  if (rc)
+    return rc;
+  rc = upload_pfsp_tables(e, ins);
+  if (rc)
+    return rc;
+  const int mm = bbk::pfsp_mm(e->m);
+  const void *k = lb == 0 ? pick_pfsp_kernel<0>(mm) : lb == 1 ? pick_pfsp_kernel<1>(mm) : pick_pfsp_kernel<2>(mm);
+  const int smem = bbk::pfsp_layout(e->m, e->T.P, lb).total;
+  rc = setup_launch(e, k, smem);
+  if (rc)
+    return rc;
+  return build_graph(e);
+}
+
+static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
+{
+  e->kind = KIND_NQ;
+  e->N = N;
+  e->G = G;
+  const int tw = bbk::nq_tail_words(N);
+  int rc = alloc_common(e, cfg, 1, tw);
+  if (rc)
+    return rc;
+  const void *k = tw == 0 ? (const void *)bbk::nq_expand<0>
+                  : tw == 1 ? (const void *)bbk::nq_expand<1> : (const void *)bbk::nq_expand<2>;
+  rc = setup_launch(e, k, 0);
+  if (rc)
+    return rc;
+  return build_graph(e);
+}
+
+extern "C" bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
+{
+  if (!ins || lb < 0 || lb > 2)
+  {
+    bb_fail(BB_ERR_ARG, "bb_pfsp_engine_create: bad instance or lower bound %d", lb);
+    return nullptr;
+  }
+  if (ins->nb_jobs > BB_MAX_JOBS || ins->nb_machines > BB_MAX_MACHINES)
+  {
+    /* the reference needs a rebuild with a larger MAX_JOBS for these (pfsp/README.md:52); refuse loudly */
+    bb_fail(BB_ERR_ARG, "instance has %d jobs x %d machines; this build supports at most %d x %d", ins->nb_jobs,
+            ins->nb_machines, BB_MAX_JOBS, BB_MAX_MACHINES);
+    return nullptr;
+  }
+  bb_engine *e = (bb_engine *)calloc(1, sizeof(bb_engine));
+  if (create_pfsp(e, ins, lb, cfg) != BB_OK)
+  {
+    bb_engine_destroy(e);
+    return nullptr;
+  }
+  if (bb_engine_reset(e, INT_MAX) != BB_OK)
+  {
+    bb_engine_destroy(e);
+    return nullptr;
+  }
+  return e;
+}
+
+extern "C" bb_engine *bb_nq_engine_create(int N, int G, const bb_config *cfg)
+{
+  if (N < 1 || N > BB_MAX_QUEENS || G < 1)
+  {
+    bb_fail(BB_ERR_ARG, "bb_nq_engine_create: need 1 <= N <= %d and G >= 1 (got N=%d G=%d)", BB_MAX_QUEENS, N, G);
+    return nullptr;
+  }
+  bb_engine *e = (bb_engine *)calloc(1, sizeof(bb_engine));
+  if (create_nq(e, N, G, cfg) != BB_OK)
+  {
+    bb_engine_destroy(e);
+    return nullptr;
+  }
+  if (bb_engine_reset(e, INT_MAX) != BB_OK)
+  {
+    bb_engine_destroy(e);
+    return nullptr;
+  }
+  return e;
+}
+
+extern "C" void bb_engine_destroy(bb_engine *e)
+{
+  if (!e)
+    return;
+  cudaSetDevice(e->device);
+  if (e->stream)
+    cudaStreamSynchronize(e->stream);
+  if (e->graph)
+    cudaGraphExecDestroy(e->graph);
+  for (int s = 0; s < 2; s++)
+  {
+    if (e->pool_mem[s])
+      cudaFree(e->pool_mem[s]);
+    if (e->tail_mem[s])
+      cudaFree(e->tail_mem[s]);
+  }
+  if (e->table_mem)
+    cudaFree(e->table_mem);
+  if (e->ctrl)
+    cudaFree(e->ctrl);
+  if (e->ctrl_h)
+    cudaFreeHost(e->ctrl_h);
+  if (e->ev0)
+    cudaEventDestroy(e->ev0);
+  if (e->ev1)
+    cudaEventDestroy(e->ev1);
+  if (e->stream)
+    cudaStreamDestroy(e->stream);
+  free(e);
+}
+
+/* ------------------------------------------------------------------ state */
+
+static int fetch_ctrl(bb_engine *e)
+{
+  BB_CUDA_TRY(cudaMemcpyAsync(e->ctrl_h, e->ctrl, sizeof(bb_ctrl), cudaMemcpyDeviceToHost, e->stream));
+  BB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  return BB_OK;
+}
+
+extern "C" int bb_engine_reset(bb_engine *e, int best)
+{
+  if (!e)
+    return bb_fail(BB_ERR_ARG, "null engine");
+  ENGINE_SET_DEVICE(e);
+  k_reset<<<1, 1, 0, e->stream>>>(e->ctrl, best, e->M, e->pool.capacity, e->kind == KIND_PFSP ? e->n : e->N);
+  BB_CUDA_TRY(cudaGetLastError());
+  e->kernel_ms = 0;
+  e->launches = 0;
+  return fetch_ctrl(e);
+}
+
+extern "C" int bb_engine_set_best(bb_engine *e, int best)
+{
+  if (!e)
+    return bb_fail(BB_ERR_ARG, "null engine");
+  ENGINE_SET_DEVICE(e);
+  k_set_best<<<1, 1, 0, e->stream>>>(e->ctrl, best);
+  BB_CUDA_TRY(cudaGetLastError());
+  return BB_OK;
+}
+
+extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int count)
+{
+  if (!e || (!host_nodes && count > 0) || count < 0)
+    return bb_fail(BB_ERR_ARG, "bb_engine_push_nodes: bad arguments");
+  if (count == 0)
+    return BB_OK;
+  ENGINE_SET_DEVICE(e);
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  const int at = e->ctrl_h->size[0];
+  if ((long long)at + count > e->pool.capacity)
+    return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while seeding %d nodes", e->pool.capacity, count);
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
+  if (e->kind == KIND_PFSP)
+  {
+    /* nodes the engine cannot represent are rejected here rather than silently mis-handled */
+    const int16_t *nd = (const int16_t *)host_nodes;
+    for (int i = 0; i < count; i++)
+      if (nd[(size_t)i * (2 + BB_MAX_JOBS)] < 0 || nd[(size_t)i * (2 + BB_MAX_JOBS)] >= e->n)
+        return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * (2 + BB_MAX_JOBS)], e->n - 1);
+  }
+  else
+  {
+    const uint8_t *nd = (const uint8_t *)host_nodes;
+    for (int i = 0; i < count; i++)
+      if (nd[(size_t)i * (1 + BB_MAX_QUEENS)] >= e->N)
+        return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * (1 + BB_MAX_QUEENS)], e->N - 1);
+  }
+  void *stage = nullptr;
+  BB_CUDA_TRY(cudaMalloc(&stage, rec * count));
+  cudaError_t err = cudaMemcpyAsync(stage, host_nodes, rec * count, cudaMemcpyHostToDevice, e->stream);
+  if (err == cudaSuccess)
+  {
+    const int blocks = (count + 127) / 128;
+    if (e->kind == KIND_PFSP)
+      k_seed_pfsp<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->T, at, e->T.mp,
+                                                 e->pool.nplanes);
+    else
+      k_seed_nq<<<blocks, 128, 0, e->stream>>>((const uint8_t *)stage, count, e->pool, e->N, at);
+    k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, count, e->grid * BB_WARPS_PER_CTA);
+    err = cudaGetLastError();
+  }
+  if (err == cudaSuccess)
+    err = cudaStreamSynchronize(e->stream);
+  cudaFree(stage);
+  if (err != cudaSuccess)
+    return bb_fail_cuda(err, "seeding", __FILE__, __LINE__);
+  return BB_OK;
+}
+
+extern "C" int bb_engine_push_root(bb_engine *e)
+{
+  if (!e)
+    return bb_fail(BB_ERR_ARG, "null engine");
+  if (e->kind == KIND_PFSP)
+  {
+    int16_t nd[2 + BB_MAX_JOBS];
+    memset(nd, 0, sizeof(nd));
+    nd[0] = 0;
+    nd[1] = -1;
+    for (int j = 0; j < e->n; j++)
+      nd[2 + j] = (int16_t)j;
+    return bb_engine_push_nodes(e, nd, 1);
+  }
+  uint8_t nd[1 + BB_MAX_QUEENS];
+  memset(nd, 0, sizeof(nd));
+  for (int j = 0; j < e->N; j++)
+    nd[1 + j] = (uint8_t)j;
+  return bb_engine_push_nodes(e, nd, 1);
+}
+
+extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long long max_count)
+{
+  if (!e || !host_nodes)
+    return bb_fail(BB_ERR_ARG, "bb_engine_export_nodes: bad arguments");
+  if (cudaSetDevice(e->device) != cudaSuccess)
+    return bb_fail(BB_ERR_CUDA, "cudaSetDevice failed");
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  const long long total = (long long)e->ctrl_h->size[0] + e->ctrl_h->size[1];
+  if (total > max_count)
+    return bb_fail(BB_ERR_ARG, "export buffer holds %lld nodes, pool has %lld", max_count, total);
+  if (total == 0)
+    return 0;
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
+  void *stage = nullptr;
+  BB_CUDA_TRY(cudaMalloc(&stage, rec * total));
+  int at = 0;
+  for (int s = 0; s < 2; s++)
+  {
+    const int cnt = e->ctrl_h->size[s];
+    if (!cnt)
+      continue;
+    const int blocks = (cnt + 127) / 128;
+    if (e->kind == KIND_PFSP)
+      k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, cnt, at);
+    else
+      k_export_nq<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, cnt, at, e->N);
+    at += cnt;
+  }
+  cudaError_t err = cudaGetLastError();
+  if (err == cudaSuccess)
+    err = cudaMemcpyAsync(host_nodes, stage, rec * total, cudaMemcpyDeviceToHost, e->stream);
+  if (err == cudaSuccess)
+    err = cudaStreamSynchronize(e->stream);
+  cudaFree(stage);
+  if (err != cudaSuccess)
+    return bb_fail_cuda(err, "export", __FILE__, __LINE__);
+  return total;
+}
+
+static void fill_stats(bb_engine *e, bb_stats *out)
+{
+  const bb_ctrl *c = e->ctrl_h;
+  out->tree = c->tree;
+  out->sol = c->sol;
+  out->parents = c->parents;
+  out->evals = c->evals;
+  out->lb2_evals = c->lb2_evals;
+  out->lb2_pairs = c->lb2_pairs;
+  out->iterations = c->iterations;
+  out->launches = e->launches;
+  out->pool_size = (long long)c->size[0] + c->size[1];
+  out->max_pool = c->max_pool;
+  out->best = c->best;
+  out->kernel_ms = e->kernel_ms;
+}
+
+extern "C" int bb_engine_get_stats(bb_engine *e, bb_stats *out)
+{
+  if (!e || !out)
+    return bb_fail(BB_ERR_ARG, "bb_engine_get_stats: bad arguments");
+  ENGINE_SET_DEVICE(e);
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  fill_stats(e, out);
+  return BB_OK;
+}
+
+/* ------------------------------------------------------------------ the device loop */
+
+extern "C" int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out)
+{
+  if (!e)
+    return bb_fail(BB_ERR_ARG, "null engine");
+  ENGINE_SET_DEVICE(e);
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  const unsigned long long it0 = e->ctrl_h->iterations;
+  while (e->ctrl_h->n > 0 && !e->ctrl_h->error)
+  {
+    long long left = max_iters > 0 ? max_iters - (long long)(e->ctrl_h->iterations - it0) : LLONG_MAX;
+    if (left <= 0)
+      break;
+    BB_CUDA_TRY(cudaEventRecord(e->ev0, e->stream));
+    if (left >= e->iters_per_launch)
+    {
+      BB_CUDA_TRY(cudaGraphLaunch(e->graph, e->stream));
+      e->launches += e->iters_per_launch;
+    }
+    else
+    {
+      for (long long i = 0; i < left; i++)
+      {
+        rc = launch_expand(e, e->stream);
+        if (rc)
+          return rc;
+      }
+      e->launches += left;
+    }
+    BB_CUDA_TRY(cudaEventRecord(e->ev1, e->stream));
+    rc = fetch_ctrl(e);
+    if (rc)
+      return rc;
+    float ms = 0;
+    BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    e->kernel_ms += ms;
+  }
+  if (out)
+    fill_stats(e, out);
+  if (e->ctrl_h->error)
+    return bb_fail(BB_ERR_OVERFLOW, "device pool overflow: capacity %d nodes per stack is too small (raise "
+                                    "bb_config.capacity or lower M)", e->pool.capacity);
+  return BB_OK;
+}
+
+/* ------------------------------------------------------------------ whole searches (single GPU here; D > 1 in bb_multi.cu) */
+
+int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N, int G, int D, int ws,
+                    const bb_config *cfg, bb_search_result *res, bb_stats *per_gpu);
+
+extern "C" int bb_pfsp_search(const bb_pfsp_instance *ins, int lb, int best0, int D, int ws, const bb_config *cfg,
+                              bb_search_result *res, bb_stats *per_gpu)
+{
+  if (!ins || !res || D < 1)
+    return bb_fail(BB_ERR_ARG, "bb_pfsp_search: bad arguments");
+  return bb_multi_search(KIND_PFSP, ins, lb, best0, 0, 0, D, ws, cfg, res, per_gpu);
+}
+
+extern "C" int bb_nq_search(int N, int G, int D, int ws, const bb_config *cfg, bb_search_result *res,
+                            bb_stats *per_gpu)
+{
+  if (!res || D < 1)
+    return bb_fail(BB_ERR_ARG, "bb_nq_search: bad arguments");
+  return bb_multi_search(KIND_NQ, nullptr, 0, INT_MAX, N, G, D, ws, cfg, res, per_gpu);
+}

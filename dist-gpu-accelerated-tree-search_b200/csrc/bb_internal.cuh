@@ -1,0 +1,95 @@
+/*
+ * bb_internal.cuh - shared device/host definitions of the native engine (not part of the C ABI).
+ *
+ * HBM layout of the node pool
+ * ---------------------------
+ * A pool is TWO LIFO stacks (ping-pong: an iteration pops a batch of parents from the top of one and appends the
+ * surviving children to the top of the other, so a batch never leaves a hole and nothing is copied twice).
+ * A stack stores fixed-size records as PLANES of 16-byte vectors: plane q of node i lives at
+ *     base + (q * capacity + i) * 16
+ * i.e. structure-of-arrays over 16-byte chunks. Thread i of a warp touching plane q of node i is a fully
+ * coalesced 512-byte uint4 access.
+ *
+ * PFSP record (32-bit words; mp = machines rounded up to even):
+ *     w0..w4   prmu[20] as uint8         (first `depth` entries = scheduled prefix)
+ *     w5       depth (byte 0)
+ *     w6..     front[mp]  uint16         completion time of the prefix on each machine (cached, not recomputed)
+ *     ..       remain[mp] uint16         total unscheduled work on each machine (cached)
+ *   -> 6 + mp words: 3 planes (48 B) at m=5, 4 planes (64 B) at m=10, 7 planes (112 B) at m=20.
+ *   limit1 is not stored (== depth-1 under the reference's forward-only branching, PFSP_node.c:9-10).
+ *
+ * N-Queens record: plane 0 = board[0..15]; N >= 16 adds a second array of `tail words` 32-bit words per node
+ *   (board[16..] then depth in the last byte); N <= 15 keeps depth in byte 15 of plane 0.
+ */
+#ifndef BB_INTERNAL_CUH
+#define BB_INTERNAL_CUH
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "bb_gpu.h"
+
+#define BB_WARPS_PER_CTA 8
+#define BB_CTA_THREADS (BB_WARPS_PER_CTA * 32)
+#define BB_TILE_MAX 32 /* parents per warp tile */
+
+/* Device-resident control block: everything an iteration needs to know is here, so iterations can be chained in
+ * a CUDA graph with no host round trip (replaces popBackBulk/pushBackBulk + the index prep of the reference). */
+struct __align__(256) bb_ctrl
+{
+  /* iteration plan, written by the last CTA of the previous iteration (or by the host when seeding) */
+  int size[2];         /* nodes in each stack */
+  int src;             /* stack this iteration pops from */
+  int n;               /* parents in this iteration's batch (0 = nothing to do) */
+  int base;            /* index of the first parent of the batch in stack src */
+  int tile;            /* parents per warp tile for this iteration */
+  unsigned int tail;   /* append cursor of stack dst = 1 - src */
+  unsigned int ticket; /* CTAs finished in this iteration */
+  /* search state */
+  int best;            /* incumbent upper bound (atomicMin) */
+  int error;           /* sticky: 1 = pool overflow */
+  int M;               /* max parents per iteration */
+  int capacity;        /* nodes per stack */
+  int max_pool;        /* high-water mark of size[0]+size[1] */
+  int maxkids;         /* most children one parent can have (jobs / queens): bounds the growth of one iteration */
+  /* counters */
+  unsigned long long tree, sol, parents, evals, lb2_evals, lb2_pairs, iterations;
+};
+
+struct bb_pool
+{
+  uint4 *planes[2];   /* per stack: [nplanes][capacity] uint4 */
+  uint32_t *tailw[2]; /* per stack: N-Queens tail words [capacity][tail_words] (may be null) */
+  int nplanes;
+  int tail_words;
+  int capacity;
+};
+
+/* instance tables in device global memory, repacked for the kernels (staged into shared memory per CTA) */
+struct bb_pfsp_dev
+{
+  int n, m, mp, P;
+  const uint8_t *p8;     /* [m][BB_MAX_JOBS] processing times (1..99), zero padded */
+  const int *tails;      /* [m] min_tails */
+  const int *heads;      /* [m] min_heads */
+  /* LB2: per (pair, slot) in Johnson order, always BB_MAX_JOBS slots (null slots have jbit = 0) */
+  const uint32_t *jbit;  /* 1 << job */
+  const int *ja;         /* p[m2][job] - p[m1][job] */
+  const int *jb;         /* lag + p[m2][job] */
+  const int2 *pairs;     /* (m1, m2) in evaluation order */
+  int best_known;
+};
+
+#define BB_CUDA_TRY(call)                                         \
+  do                                                              \
+  {                                                               \
+    cudaError_t err__ = (call);                                   \
+    if (err__ != cudaSuccess)                                     \
+      return bb_fail_cuda(err__, #call, __FILE__, __LINE__);      \
+  } while (0)
+
+int bb_fail_cuda(cudaError_t err, const char *what, const char *file, int line);
+int bb_fail(int code, const char *fmt, ...);
+void bb_note_cuda(cudaError_t err, const char *what);
+
+#endif

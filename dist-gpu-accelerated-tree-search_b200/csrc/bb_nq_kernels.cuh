@@ -1,0 +1,172 @@
+/*
+ * bb_nq_kernels.cuh - fused evaluate -> branch -> compact for N-Queens on the device-resident pool (sm_100a).
+ *
+ * One launch = one pool iteration = the reference's per-batch popBack loop + H2D + evaluate_gpu + D2H labels +
+ * generate_children + pushBack (nqueens/nqueens_multigpu_cuda.cu:288-314, kernel :158-186, branch :189-210).
+ *
+ * Same warp-tile mapping as the PFSP kernel: a warp loads <= 32 parents (coalesced), prefix-sums N - depth, then
+ * evaluates the candidate slots 32 at a time with one lane per (parent, slot). isSafe is the reference's diagonal
+ * test on int-promoted values (nqueens_c.c:80-96), really executed G times per placed queen (-g is the
+ * reference's arithmetic-intensity knob, README "safety checks per evaluation").
+ *
+ * Children at depth N are solutions: the reference pushes them, counts them in exploredTree, and counts
+ * exploredSol when they are popped (nqueens_c.c:103-105, 112-113). Here they are counted in both at generation and
+ * never written to HBM.
+ *
+ * Record: plane 0 (uint4) = board[0..15]; N <= 15 keeps depth in byte 15; N >= 16 adds TW 32-bit tail words per
+ * node holding board[16..N-1] followed by depth at tail byte N-16.
+ */
+#ifndef BB_NQ_KERNELS_CUH
+#define BB_NQ_KERNELS_CUH
+
+#include "bb_internal.cuh"
+#include "bb_pfsp_kernels.cuh"
+
+namespace bbk
+{
+
+__host__ __device__ inline int nq_tail_words(int N) { return N <= 15 ? 0 : (N - 16 + 1 + 3) / 4; }
+
+template <int TW>
+__global__ void __launch_bounds__(BB_CTA_THREADS, 4)
+nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+{
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int cap = pool.capacity;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base, TS = ctrl->tile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int dbyte = TW ? 16 + (N - 16) : 15; /* where depth lives in the 16 + 4*TW byte record */
+
+  /* per warp: 32 rows of 32 bytes (board bytes 0..23 used), offsets [33] */
+  __shared__ __align__(16) unsigned char rows_s[BB_WARPS_PER_CTA][32 * 32];
+  __shared__ int offs_all[BB_WARPS_PER_CTA][36];
+  unsigned char *rows = rows_s[warp];
+  int *offs_s = offs_all[warp];
+
+  const uint4 *__restrict__ splane = pool.planes[src];
+  uint4 *__restrict__ dplane = pool.planes[dst];
+  const uint32_t *__restrict__ stail = pool.tailw[src];
+  uint32_t *__restrict__ dtail = pool.tailw[dst];
+
+  unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
+
+  const int ntiles = (nbatch + TS - 1) / TS;
+  for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += gridDim.x * BB_WARPS_PER_CTA)
+  {
+    const int first = tile * TS;
+    const int cnt = min(TS, nbatch - first);
+    int kids = 0;
+    if (lane < cnt)
+    {
+      const size_t node = (size_t)base + first + lane;
+      *reinterpret_cast<uint4 *>(rows + lane * 32) = splane[node];
+#pragma unroll
+      for (int t = 0; t < TW; t++)
+        *reinterpret_cast<uint32_t *>(rows + lane * 32 + 16 + 4 * t) = stail[node * TW + t];
+      kids = N - (int)rows[lane * 32 + dbyte];
+    }
+    const int incl = warp_incl_scan(kids, lane);
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    offs_s[lane] = incl - kids;
+    if (lane == 0)
+    {
+      offs_s[32] = total;
+      cnt6[2] += cnt;
+      cnt6[3] += total;
+    }
+    __syncwarp();
+
+    for (int c0 = 0; c0 < total; c0 += 32)
+    {
+      const int c = c0 + lane;
+      const bool act = c < total;
+      int p = 0;
+      if (act)
+      {
+#pragma unroll
+        for (int st = 16; st > 0; st >>= 1)
+          if (offs_s[p + st] <= c)
+            p += st;
+      }
+      const unsigned char *row = rows + p * 32;
+      const int depth = row[dbyte];
+      const int k = act ? depth + (c - offs_s[p]) : depth;
+      const int cand = row[k]; /* row position tried for column `depth` */
+
+      /* isSafe: nqueens_c.c:80-96 / nqueens_multigpu_cuda.cu:170-183 */
+      int safe = 1;
+      for (int i = 0; i < depth; i++)
+      {
+        int other = row[i];
+        const int d = depth - i;
+        for (int g = 0; g < G; g++)
+        {
+          asm volatile("" : "+r"(other)); /* keep the G repetitions as real work, as the reference's -g intends */
+          safe &= (other != cand - d) & (other != cand + d);
+        }
+      }
+      const bool ok = act && safe;
+      const bool leaf = (depth + 1 == N);
+      if (ok)
+      {
+        cnt6[0]++; /* exploredTree counts every safe placement, leaves included */
+        if (leaf)
+          cnt6[1]++;
+      }
+      const bool keep = ok && !leaf;
+      const unsigned kmask = __ballot_sync(0xffffffffu, keep);
+      if (kmask)
+      {
+        const int nk = __popc(kmask);
+        unsigned pos = 0;
+        if (lane == 0)
+          pos = atomicAdd(&ctrl->tail, (unsigned)nk);
+        pos = __shfl_sync(0xffffffffu, pos, 0);
+        if (pos + (unsigned)nk > (unsigned)cap)
+        {
+          if (lane == 0)
+            atomicExch(&ctrl->error, 1);
+        }
+        else if (keep)
+        {
+          const size_t slot = (size_t)pos + __popc(kmask & ((1u << lane) - 1u));
+          uint32_t w[4 + (TW ? TW : 1)];
+          const uint4 q0 = *reinterpret_cast<const uint4 *>(row);
+          w[0] = q0.x;
+          w[1] = q0.y;
+          w[2] = q0.z;
+          w[3] = q0.w;
+#pragma unroll
+          for (int t = 0; t < TW; t++)
+            w[4 + t] = *reinterpret_cast<const uint32_t *>(row + 16 + 4 * t);
+          /* swap board[depth] <-> board[k] (xor patch), then depth+1 (depth byte xor old^new) */
+          const uint32_t x = (uint32_t)(cand ^ row[depth]);
+          const uint32_t dx = (uint32_t)(depth ^ (depth + 1));
+#pragma unroll
+          for (int wi = 0; wi < 4 + TW; wi++)
+          {
+            uint32_t patch = 0;
+            if (wi == (depth >> 2))
+              patch ^= x << (8 * (depth & 3));
+            if (wi == (k >> 2))
+              patch ^= x << (8 * (k & 3));
+            if (wi == (dbyte >> 2))
+              patch ^= dx << (8 * (dbyte & 3));
+            w[wi] ^= patch;
+          }
+          dplane[slot] = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+          for (int t = 0; t < TW; t++)
+            dtail[slot * TW + t] = w[4 + t];
+        }
+      }
+    }
+    __syncwarp();
+  }
+  finish_iteration(ctrl, cnt6, src, base, cap);
+}
+
+} // namespace bbk
+#endif

@@ -1,0 +1,222 @@
+/*
+ * bb_gpu.h - C ABI of libbbgpu.so: the B200-native (sm_100a) bound -> prune -> branch engine.
+ *
+ * Two levels, both plain C (pointers + sizes, no C++/torch types):
+ *
+ *  1. COMPAT level  - the exact extern "C" symbols the reference's C drivers bind
+ *                     (pfsp/lib/PFSP_gpu_lib.cuh:13-29), so pfsp_multigpu_cuda.c links against this library
+ *                     unchanged, plus the analogous N-Queens entry the reference keeps inside its .cu driver.
+ *  2. NATIVE level  - a device-resident structure-of-arrays node pool per GPU with the whole
+ *                     bound+prune+branch+compaction loop on the device; host code only seeds, polls, steals.
+ *
+ * File:line citations are relative to the reference tree (ivantag13/dist-GPU-accelerated-tree-search).
+ * Every int-returning function returns 0 on success and a negative code on failure; bb_last_error() gives the
+ * message for the calling thread. There is NO CPU fallback anywhere in this library: without a CUDA device every
+ * compute entry point fails with BB_ERR_CUDA.
+ */
+#ifndef BB_GPU_H
+#define BB_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BB_MAX_JOBS 20     /* pfsp/lib/macro.h:10 */
+#define BB_MAX_MACHINES 20 /* pfsp/lib/macro.h:11 */
+#define BB_MAX_QUEENS 20   /* nqueens/lib/NQueens_node.h:11 */
+
+enum
+{
+  BB_OK = 0,
+  BB_ERR_ARG = -1,      /* bad argument (size, null pointer, unsupported instance class) */
+  BB_ERR_CUDA = -2,     /* a CUDA call failed; bb_last_cuda_error() holds the cudaError_t */
+  BB_ERR_OVERFLOW = -3, /* device pool capacity exceeded */
+  BB_ERR_STATE = -4     /* call not valid in the engine's current state */
+};
+
+const char *bb_last_error(void);
+int bb_last_cuda_error(void);
+
+/* =====================================================================================================
+ * COMPAT LEVEL (drop-in for pfsp/lib/PFSP_gpu_lib.cu)
+ * The struct layouts are the reference's; when the reference's own headers are included first their
+ * definitions are used.
+ * ===================================================================================================== */
+
+#ifndef C_BOUND_SIMPLE_H_ /* pfsp/lib/c_bound_simple.h:14-21 */
+typedef struct lb1_bound_data
+{
+  int *p_times;
+  int *min_heads;
+  int *min_tails;
+  int nb_jobs;
+  int nb_machines;
+} lb1_bound_data;
+#endif
+
+#ifndef C_BOUND_JOHNSON_H /* pfsp/lib/c_bound_johnson.h:16-27 */
+typedef struct lb2_bound_data
+{
+  int *johnson_schedules;
+  int *lags;
+  int *machine_pairs_1;
+  int *machine_pairs_2;
+  int *machine_pair_order;
+  int nb_machine_pairs;
+  int nb_jobs;
+  int nb_machines;
+} lb2_bound_data;
+#endif
+
+#if !defined(PFSP_NODE_H) && !defined(NQUEENS_NODE_H) /* pfsp/lib/PFSP_node.h:15-20 : 44-byte AoS node */
+typedef struct
+{
+  int16_t depth;
+  int16_t limit1;
+  int16_t prmu[BB_MAX_JOBS];
+} Node;
+#endif
+
+/* nqueens/lib/NQueens_node.h:13-17 : 21-byte node. (Named apart: the reference reuses the name `Node`.) */
+typedef struct
+{
+  uint8_t depth;
+  uint8_t board[BB_MAX_QUEENS];
+} bb_nq_node;
+
+/* Replaces PFSP_gpu_lib.cu:129-152 (called at pfsp_multigpu_cuda.c:295). Launches, does not synchronise.
+ * lb: 0 = LB1_d over parentsSize parents, 1 = LB1 / 2 = LB2 over `size` children. All pointers except `best`
+ * are device pointers owned by the caller; `best` is a host pointer read once. bounds[] layout and values are
+ * bit-identical to the reference kernels, including the LB2 early-exit value. */
+void evaluate_gpu(const int jobs, const int lb, const int size, const int nbBlocks, const int parentsSize,
+                  int *best, const lb1_bound_data lbound1, const lb2_bound_data lbound2, Node *parents,
+                  int *bounds, int *sumOffSets_d, int *nodeIndex_d);
+
+/* Replace PFSP_gpu_lib.cu:154-200 (called at pfsp_multigpu_cuda.c:190,194): device deep copy of the host
+ * tables. As in the reference the trailing pointer arguments are passed by value and ignored. */
+void lb1_alloc_gpu(lb1_bound_data *lbound1_d, lb1_bound_data *lbound1, int *p_times_d, int *min_heads_d,
+                   int *min_tails_d, int jobs, int machines);
+void lb2_alloc_gpu(lb2_bound_data *lbound2_d, lb2_bound_data *lbound2, int *johnson_schedule_d, int *lags_d,
+                   int *machine_pairs_1_d, int *machine_pairs_2_d, int *machine_pair_order_d, int jobs,
+                   int machines);
+
+/* The authors' op/byte model, PFSP_gpu_lib.cu:213-267. */
+int P_of(int M);
+int flop_lb1(int N, int M, int lim);
+int bytes_per_inv_lb1(int N, int M);
+int flop_lb2(int N, int M, int lim);
+int bytes_per_inv_lb2(int N, int M, int lim);
+
+/* Replaces the kernel + launch the reference keeps inside its driver (nqueens_multigpu_cuda.cu:158-186,
+ * launched at :301): labels_d[k + i*N] for slot k >= depth of parent i; slots below depth are not written. */
+void nq_evaluate_gpu(const int N, const int G, const bb_nq_node *parents_d, uint8_t *labels_d, const int size);
+
+/* =====================================================================================================
+ * HOST PRECOMPUTE (C, no GPU): replaces c_taillard.c:46-105, c_bound_simple.c:277-322,
+ * c_bound_johnson.c:48-178. Tables are bit-identical to the reference's (tests compare FNV hashes).
+ * ===================================================================================================== */
+
+typedef struct bb_pfsp_instance
+{
+  int nb_jobs;
+  int nb_machines;
+  int nb_machine_pairs;
+  int best_known;          /* Taillard best-known makespan, or INT_MAX for custom matrices */
+  int inst;                /* Taillard id 1..120, 0 for custom */
+  int *p_times;            /* [machines*jobs] machine-major */
+  int *min_heads;          /* [machines] */
+  int *min_tails;          /* [machines] */
+  int *machine_pairs_1;    /* [pairs] */
+  int *machine_pairs_2;    /* [pairs] */
+  int *machine_pair_order; /* [pairs] */
+  int *lags;               /* [pairs*jobs] */
+  int *johnson_schedules;  /* [pairs*jobs] */
+} bb_pfsp_instance;
+
+int bb_taillard_nb_jobs(int inst);
+int bb_taillard_nb_machines(int inst);
+int bb_taillard_best_ub(int inst);
+long bb_taillard_seed(int inst);
+void bb_taillard_processing_times(int inst, int *ptm);
+bb_pfsp_instance *bb_pfsp_instance_taillard(int inst);
+bb_pfsp_instance *bb_pfsp_instance_from_ptimes(int nb_jobs, int nb_machines, const int *p_times);
+void bb_pfsp_instance_free(bb_pfsp_instance *ins);
+
+/* =====================================================================================================
+ * NATIVE LEVEL: device-resident pool engine (one per GPU)
+ * Replaces the host pool (Pool_atom.c), the per-batch PCIe round trip and index prep
+ * (pfsp_multigpu_cuda.c:227-230, 275-301), host prune+branch (PFSP_lib.h:51-95,
+ * nqueens_multigpu_cuda.cu:189-210) and the CPU warm-up / drain steps (pfsp_multigpu_cuda.c:111-118, 487-495).
+ * ===================================================================================================== */
+
+typedef struct bb_engine bb_engine;
+
+typedef struct bb_config
+{
+  int device;             /* CUDA device ordinal */
+  int M;                  /* max parents per device iteration (-M, PFSP_lib.c:252-259); <=0: 50000 */
+  int m;                  /* min pool size a worker keeps when asked to share (-m); <=0: 25 */
+  long long capacity;     /* nodes per stack (two stacks are allocated); <=0: chosen from M */
+  int iters_per_launch;   /* device iterations chained in one CUDA-graph launch; <=0: 32 */
+  int lb2_prefilter;      /* LB2 only: 1 = skip the pair loop for children LB1_d already prunes (default 1) */
+} bb_config;
+
+typedef struct bb_stats
+{
+  unsigned long long tree;        /* exploredTree increments made on this device */
+  unsigned long long sol;         /* exploredSol increments */
+  unsigned long long parents;     /* nodes popped and decomposed */
+  unsigned long long evals;       /* child bounds / safety evaluations */
+  unsigned long long lb2_evals;   /* children that entered the LB2 pair loop */
+  unsigned long long lb2_pairs;   /* machine pairs evaluated in total */
+  unsigned long long iterations;  /* non-empty device iterations */
+  unsigned long long launches;    /* kernels launched by this engine */
+  long long pool_size;            /* nodes left in the pool */
+  long long max_pool;             /* high-water mark */
+  int best;                       /* incumbent */
+  double kernel_ms;               /* CUDA-event time of all expand kernels (launching stream) */
+} bb_stats;
+
+void bb_config_default(bb_config *cfg);
+
+/* lb: 0 LB1_d, 1 LB1, 2 LB2 (PFSP_lib.c:225-232). Uploads the tables (a6) and allocates the pool. */
+bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb, const bb_config *cfg);
+bb_engine *bb_nq_engine_create(int N, int G, const bb_config *cfg);
+void bb_engine_destroy(bb_engine *e);
+
+int bb_engine_reset(bb_engine *e, int best);            /* empty pool, zero counters, set incumbent */
+int bb_engine_push_root(bb_engine *e);                  /* initRoot: PFSP_node.c:7-14 / NQueens_node.c:7-13 */
+/* Seed from HOST nodes in the reference's AoS layouts (Node / bb_nq_node); the engine derives its cached
+ * per-node state on the device. */
+int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int count);
+/* Copy the pool back to HOST in the reference's AoS layout (tests, checkpointing). Returns the count. */
+long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long long max_count);
+int bb_engine_set_best(bb_engine *e, int best);
+int bb_engine_get_stats(bb_engine *e, bb_stats *out);
+
+/* Run device iterations until the pool is empty (max_iters <= 0) or max_iters iterations were done. */
+int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out);
+
+/* Whole search on D GPUs of this process (one host thread per GPU, peer-memory work stealing when ws != 0):
+ * the equivalent of pfsp_search() / nqueens_search() in the reference drivers. per_gpu may be NULL or [D]. */
+typedef struct bb_search_result
+{
+  unsigned long long tree;
+  unsigned long long sol;
+  int best;
+  double elapsed_s;     /* wall time of the whole search */
+  double kernel_ms_max; /* max over GPUs of device time in expand kernels */
+  unsigned long long steals, steals_ok;
+} bb_search_result;
+
+int bb_pfsp_search(const bb_pfsp_instance *ins, int lb, int best0, int D, int ws, const bb_config *cfg,
+                   bb_search_result *res, bb_stats *per_gpu);
+int bb_nq_search(int N, int G, int D, int ws, const bb_config *cfg, bb_search_result *res, bb_stats *per_gpu);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BB_GPU_H */
