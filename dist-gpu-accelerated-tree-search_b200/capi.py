@@ -57,7 +57,9 @@ class Stats(C.Structure):
     _fields_ = [("tree", C.c_ulonglong), ("sol", C.c_ulonglong), ("parents", C.c_ulonglong),
                 ("evals", C.c_ulonglong), ("lb2_evals", C.c_ulonglong), ("lb2_pairs", C.c_ulonglong),
                 ("iterations", C.c_ulonglong), ("launches", C.c_ulonglong), ("pool_size", C.c_longlong),
-                ("max_pool", C.c_longlong), ("best", C.c_int), ("kernel_ms", C.c_double)]
+                ("max_pool", C.c_longlong), ("best", C.c_int), ("kernel_ms", C.c_double), ("span_ms", C.c_double),
+                ("h2d_bytes", C.c_ulonglong), ("d2h_bytes", C.c_ulonglong), ("table_bytes", C.c_ulonglong),
+                ("grid", C.c_int), ("smem_bytes", C.c_int), ("record_bytes", C.c_int)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

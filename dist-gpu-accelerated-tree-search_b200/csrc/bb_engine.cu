@@ -75,6 +75,7 @@ struct bb_engine
   bb_pfsp_dev T;
   void *table_mem;
   int lb, n, m, prefilter;
+  unsigned long long table_bytes;
   /* N-Queens */
   int N, G;
   /* launch */
@@ -82,8 +83,9 @@ struct bb_engine
   int grid, smem;
   int iters_per_launch;
   cudaGraphExec_t graph;
-  cudaEvent_t ev0, ev1;
-  double kernel_ms;
+  cudaEvent_t ev0, ev1, ev_begin, ev_end;
+  double kernel_ms, span_ms;
+  unsigned long long h2d_bytes, d2h_bytes;
   unsigned long long launches;
   int M, m_keep;
 };
@@ -273,6 +275,8 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   BB_CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
   BB_CUDA_TRY(cudaEventCreate(&e->ev0));
   BB_CUDA_TRY(cudaEventCreate(&e->ev1));
+  BB_CUDA_TRY(cudaEventCreate(&e->ev_begin));
+  BB_CUDA_TRY(cudaEventCreate(&e->ev_end));
   BB_CUDA_TRY(cudaMalloc(&e->ctrl, sizeof(bb_ctrl)));
   BB_CUDA_TRY(cudaMallocHost(&e->ctrl_h, sizeof(bb_ctrl)));
   e->pool.capacity = (int)capacity;
@@ -400,6 +404,7 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   }
   BB_CUDA_TRY(cudaMalloc(&e->table_mem, total));
   BB_CUDA_TRY(cudaMemcpy(e->table_mem, h.data(), total, cudaMemcpyHostToDevice));
+  e->table_bytes = total;
   unsigned char *d = (unsigned char *)e->table_mem;
   e->T.n = n;
   e->T.m = m;
@@ -530,6 +535,10 @@ extern "C" void bb_engine_destroy(bb_engine *e)
     cudaEventDestroy(e->ev0);
   if (e->ev1)
     cudaEventDestroy(e->ev1);
+  if (e->ev_begin)
+    cudaEventDestroy(e->ev_begin);
+  if (e->ev_end)
+    cudaEventDestroy(e->ev_end);
   if (e->stream)
     cudaStreamDestroy(e->stream);
   free(e);
@@ -541,6 +550,7 @@ static int fetch_ctrl(bb_engine *e)
 {
   BB_CUDA_TRY(cudaMemcpyAsync(e->ctrl_h, e->ctrl, sizeof(bb_ctrl), cudaMemcpyDeviceToHost, e->stream));
   BB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+  e->d2h_bytes += sizeof(bb_ctrl);
   return BB_OK;
 }
 
@@ -552,7 +562,10 @@ extern "C" int bb_engine_reset(bb_engine *e, int best)
   k_reset<<<1, 1, 0, e->stream>>>(e->ctrl, best, e->M, e->pool.capacity, e->kind == KIND_PFSP ? e->n : e->N);
   BB_CUDA_TRY(cudaGetLastError());
   e->kernel_ms = 0;
+  e->span_ms = 0;
   e->launches = 0;
+  e->h2d_bytes = 0;
+  e->d2h_bytes = 0;
   return fetch_ctrl(e);
 }
 
@@ -598,6 +611,7 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
   void *stage = nullptr;
   BB_CUDA_TRY(cudaMalloc(&stage, rec * count));
   cudaError_t err = cudaMemcpyAsync(stage, host_nodes, rec * count, cudaMemcpyHostToDevice, e->stream);
+  e->h2d_bytes += rec * count;
   if (err == cudaSuccess)
   {
     const int blocks = (count + 127) / 128;
@@ -694,6 +708,13 @@ static void fill_stats(bb_engine *e, bb_stats *out)
   out->max_pool = c->max_pool;
   out->best = c->best;
   out->kernel_ms = e->kernel_ms;
+  out->span_ms = e->span_ms;
+  out->h2d_bytes = e->h2d_bytes;
+  out->d2h_bytes = e->d2h_bytes;
+  out->table_bytes = e->table_bytes;
+  out->grid = e->grid;
+  out->smem_bytes = e->smem;
+  out->record_bytes = e->pool.nplanes * 16 + e->pool.tail_words * 4;
 }
 
 extern "C" int bb_engine_get_stats(bb_engine *e, bb_stats *out)
@@ -719,6 +740,7 @@ extern "C" int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out)
   if (rc)
     return rc;
   const unsigned long long it0 = e->ctrl_h->iterations;
+  BB_CUDA_TRY(cudaEventRecord(e->ev_begin, e->stream));
   while (e->ctrl_h->n > 0 && !e->ctrl_h->error)
   {
     long long left = max_iters > 0 ? max_iters - (long long)(e->ctrl_h->iterations - it0) : LLONG_MAX;
@@ -747,6 +769,13 @@ extern "C" int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out)
     float ms = 0;
     BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
     e->kernel_ms += ms;
+  }
+  BB_CUDA_TRY(cudaEventRecord(e->ev_end, e->stream));
+  BB_CUDA_TRY(cudaEventSynchronize(e->ev_end));
+  {
+    float ms = 0;
+    BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
+    e->span_ms += ms;
   }
   if (out)
     fill_stats(e, out);

@@ -177,7 +177,14 @@ typedef struct bb_stats
   long long pool_size;            /* nodes left in the pool */
   long long max_pool;             /* high-water mark */
   int best;                       /* incumbent */
-  double kernel_ms;               /* CUDA-event time of all expand kernels (launching stream) */
+  double kernel_ms;               /* CUDA-event time of all expand launches (events on the launching stream) */
+  double span_ms;                 /* CUDA-event time from the first to the last launch of bb_engine_run calls */
+  unsigned long long h2d_bytes;   /* host->device bytes copied since the last reset (seeded nodes) */
+  unsigned long long d2h_bytes;   /* device->host bytes copied since the last reset (control-block polls) */
+  unsigned long long table_bytes; /* instance tables uploaded at creation */
+  int grid;                       /* CTAs per launch (a multiple of the SM count) */
+  int smem_bytes;                 /* dynamic shared memory per CTA */
+  int record_bytes;               /* bytes one node occupies in the device pool */
 } bb_stats;
 
 void bb_config_default(bb_config *cfg);

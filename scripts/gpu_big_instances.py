@@ -1,4 +1,5 @@
 import sys, time
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from __graft_entry__ import load_package
 bb=load_package()
 def run_pfsp(inst,lb,M,**kw):

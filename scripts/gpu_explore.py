@@ -1,5 +1,7 @@
+import os
 import sys, time, ctypes as C
-sys.path.insert(0,'tests')
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),'tests'))
+import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from __graft_entry__ import load_package
 bb=load_package()
 def run_pfsp(inst,lb,M,exp=None,**kw):

@@ -1,0 +1,185 @@
+"""GPU parity of the native device-resident engine (bb_engine_* / bb_pfsp_search / bb_nq_search through the C ABI)
+against the CPU oracle and the golden counts produced by the compiled reference."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import orc
+from __graft_entry__ import load_package
+
+pytestmark = pytest.mark.gpu
+bb = load_package()
+INT_MAX = 2**31 - 1
+
+
+def node_set(a, width):
+    return sorted(tuple(int(v) for v in r[:width]) for r in a)
+
+
+def oracle_one_level(inst_handle, n, lb, parents, best):
+    L = orc.oracle()
+    nb = int((n - parents[:, 0]).sum())
+    bounds = np.zeros(max(nb, 1), np.int32)
+    L.orc_evaluate_chunk(inst_handle, lb, parents, len(parents), best, bounds)
+    tree, sol, b = C.c_ulonglong(0), C.c_ulonglong(0), C.c_int(best)
+    kids = np.zeros((max(nb, 1), orc.NODE_I16), np.int16)
+    k = L.orc_generate_children(parents, len(parents), n, bounds, C.byref(tree), C.byref(sol), C.byref(b), kids)
+    return kids[:k], tree.value, sol.value, b.value, nb
+
+
+@pytest.mark.parametrize("inst", [1, 14, 21])
+@pytest.mark.parametrize("lb", [0, 1, 2])
+def test_one_iteration_children_match_oracle(inst, lb):
+    """bound + prune + branch of one batch == evaluate_gpu + generate_children of the reference (as a set:
+    the device appends survivors in warp order)"""
+    L = orc.oracle()
+    ins = bb.Instance(inst=inst)
+    n = ins.n
+    h = L.orc_pfsp_new(inst)
+    rng = np.random.default_rng(100 * inst + lb)
+    eng = bb.Engine.pfsp(ins, lb, M=100000)
+    for best in (ins.best_known, ins.best_known + 150, ins.best_known - 30):
+        parents = orc.random_pfsp_nodes(rng, n, 5000, 0, n - 2)  # inner nodes only: `best` stays constant
+        parents[0, :2] = (0, -1)
+        parents[0, 2:2 + n] = np.arange(n)
+        eng.reset(best)
+        eng.push_nodes(parents)
+        assert node_set(eng.export_nodes(), 2 + n) == node_set(parents, 2 + n)  # seed/export round trip
+        st = eng.run(1)
+        kids, tree, sol, b, nb = oracle_one_level(h, n, lb, parents, best)
+        assert (st.tree, st.sol, st.best, st.parents, st.evals) == (tree, sol, b, len(parents), nb)
+        assert st.pool_size == len(kids)
+        assert node_set(eng.export_nodes(), 2 + n) == node_set(kids, 2 + n)
+    eng.close()
+    L.orc_pfsp_free(h)
+
+
+def test_leaves_update_incumbent():
+    """parents one job short of complete: every child is a leaf, counts a solution, and the best makespan wins
+    (PFSP_lib.h:64-71); with ub = inf this is how -u 0 finds the optimum"""
+    L = orc.oracle()
+    ins = bb.Instance(inst=14)
+    h = L.orc_pfsp_new(14)
+    rng = np.random.default_rng(8)
+    parents = orc.random_pfsp_nodes(rng, 20, 3000, 19, 19)
+    exp_best = min(L.orc_makespan(h, p[2:].astype(np.int32).copy()) for p in parents)
+    for lb in (0, 1, 2):
+        eng = bb.Engine.pfsp(ins, lb)
+        eng.reset(INT_MAX)
+        eng.push_nodes(parents)
+        st = eng.run(0)
+        assert (st.sol, st.tree, st.best, st.pool_size) == (3000, 0, exp_best, 0)
+        eng.close()
+    L.orc_pfsp_free(h)
+
+
+def test_full_runs_match_reference_counts(golden):
+    g = golden("runs")
+    for r in g["pfsp"] + [s for s in g["survey"]["pfsp"] if s["tree"] < 200_000_000]:
+        ins = bb.Instance(inst=r["inst"])
+        res, per = bb.pfsp_search(ins, r["lb"], M=200000)
+        assert (res.tree, res.sol, res.best) == (r["tree"], r["sol"], r["makespan"]), r
+        assert per[0].parents == res.tree + 1  # every explored node is decomposed exactly once, plus the root
+        assert per[0].pool_size == 0
+
+
+@pytest.mark.parametrize("M,iters", [(25, 8), (1000, 32), (50000, 32), (1 << 20, 1)])
+def test_counts_do_not_depend_on_batching(M, iters):
+    ins = bb.Instance(inst=14)
+    for lb, exp in ((1, (2573652, 2648, 1377)), (2, (144639, 0, 1377))):
+        if M == 25 and lb == 1:
+            continue  # 100k+ tiny iterations: covered by LB2 at this size
+        res, _ = bb.pfsp_search(ins, lb, M=M, iters_per_launch=iters)
+        assert (res.tree, res.sol, res.best) == exp
+
+
+def test_lb2_prefilter_does_not_change_counts():
+    ins = bb.Instance(inst=14)
+    a, pa = bb.pfsp_search(ins, 2, lb2_prefilter=1)
+    b, pb = bb.pfsp_search(ins, 2, lb2_prefilter=0)
+    assert (a.tree, a.sol, a.best) == (b.tree, b.sol, b.best) == (144639, 0, 1377)
+    assert pb[0].lb2_evals == pb[0].evals == 1298094 > pa[0].lb2_evals  # SURVEY appendix A.2 census
+
+
+def test_custom_instance_generic_kernel_and_unknown_optimum():
+    """a 9x7 matrix exercises the runtime-m kernel; start from ub = inf to find the optimum, then both
+    implementations must walk the same tree from ub = optimum"""
+    L = orc.oracle()
+    rng = np.random.default_rng(42)
+    p = rng.integers(1, 100, size=(7, 9)).astype(np.int32)
+    ins = bb.Instance(p_times=p)
+    h = L.orc_pfsp_from_ptimes(9, 7, np.ascontiguousarray(p.reshape(-1)))
+    st = orc.RunStats()
+    L.orc_pfsp_search(h, 0, INT_MAX, 0, C.byref(st))
+    opt = st.best
+    for lb in (0, 1, 2):
+        res, _ = bb.pfsp_search(ins, lb, best0=INT_MAX)
+        assert res.best == opt                       # -u 0: only the optimum is pinned
+        L.orc_pfsp_search(h, lb, opt, 0, C.byref(st))
+        res, _ = bb.pfsp_search(ins, lb, best0=opt)
+        assert (res.tree, res.sol, res.best) == (st.tree, st.sol, opt)
+    L.orc_pfsp_free(h)
+
+
+def test_small_capacity_is_safe():
+    """near capacity the planner shrinks batches; if even that cannot fit the engine reports BB_ERR_OVERFLOW.
+    It never returns wrong counts."""
+    ins = bb.Instance(inst=14)
+    try:
+        res, _ = bb.pfsp_search(ins, 1, M=50000, capacity=120000)
+        assert (res.tree, res.sol, res.best) == (2573652, 2648, 1377)
+    except bb.BBError as ex:
+        assert "overflow" in str(ex)
+    try:  # a pool of 1024 nodes per stack: batches shrink to ~50 parents, still exact
+        res, per = bb.pfsp_search(ins, 2, M=50000, capacity=1024)
+        assert (res.tree, res.sol, res.best) == (144639, 0, 1377) and per[0].max_pool <= 2048
+    except bb.BBError as ex:
+        assert "overflow" in str(ex)
+    with pytest.raises(bb.BBError, match="too small"):
+        bb.pfsp_search(ins, 1, capacity=100)
+
+
+@pytest.mark.parametrize("N", [1, 2, 3, 4, 8, 12, 14, 15, 16, 17, 20])
+def test_nqueens_one_iteration_matches_oracle(N):
+    L = orc.oracle()
+    rng = np.random.default_rng(N)
+    nodes = orc.random_nq_nodes(rng, N, 4000, 0, max(N - 1, 0))
+    labels = np.zeros(len(nodes) * N, np.uint8)
+    L.orc_nq_labels(N, 1, nodes, len(nodes), labels)
+    tree, sol = C.c_ulonglong(0), C.c_ulonglong(0)
+    kids = np.zeros((len(nodes) * N, orc.NQ_REC), np.uint8)
+    k = L.orc_nq_generate_children(N, nodes, len(nodes), labels, C.byref(tree), C.byref(sol), kids)
+    inner = kids[:k][kids[:k, 0] < N]
+    eng = bb.Engine.nqueens(N, 1)
+    eng.reset()
+    eng.push_nodes(nodes)
+    assert node_set(eng.export_nodes(), 1 + N) == node_set(nodes, 1 + N)
+    st = eng.run(1)
+    # depth-N children are counted (tree and sol) but not stored
+    assert st.tree == tree.value and st.sol == k - len(inner) and st.pool_size == len(inner)
+    assert node_set(eng.export_nodes(), 1 + N) == node_set(inner, 1 + N)
+    eng.close()
+
+
+def test_nqueens_counts(golden):
+    g = golden("runs")
+    for r in g["nqueens"] + [s for s in g["survey"]["nqueens"] if s["N"] <= 16]:
+        for G in ((1, 4) if r["N"] <= 12 else (1,)):
+            res, per = bb.nq_search(r["N"], G, M=1 << 20)
+            assert (res.tree, res.sol) == (r["tree"], r["sol"]), r
+            assert per[0].parents == res.tree - res.sol + 1
+
+
+def test_nqueens_17_full_size(golden):
+    r = [s for s in golden("runs")["survey"]["nqueens"] if s["N"] == 17][0]
+    res, _ = bb.nq_search(17, 1, M=1 << 22)
+    assert (res.tree, res.sol) == (r["tree"], r["sol"]) == (8017021931, 95815104)
+
+
+def test_pfsp_full_size_properties():
+    """ta022 / LB1_d, 711 M nodes: counts from the reference run"""
+    ins = bb.Instance(inst=22)
+    res, per = bb.pfsp_search(ins, 0, M=1 << 20)
+    assert (res.tree, res.sol, res.best) == (711291688, 4346, 2099)
+    assert per[0].parents == res.tree + 1
