@@ -81,7 +81,7 @@ EXPORTS = [
     "bb_pfsp_instance_taillard", "bb_pfsp_instance_from_ptimes", "bb_pfsp_instance_free", "bb_config_default",
     "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_engine_reset", "bb_engine_push_root",
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
-    "bb_pfsp_search", "bb_nq_search",
+    "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static",
 ]
 
 lib.bb_last_error.restype = C.c_char_p
@@ -110,6 +110,8 @@ lib.bb_pfsp_search.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, C.c_in
                                C.POINTER(SearchResult), C.POINTER(Stats)]
 lib.bb_nq_search.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Config), C.POINTER(SearchResult),
                              C.POINTER(Stats)]
+lib.bb_pfsp_expand_static.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp]
+STATIC_MAX_PARENTS = 2048  # BB_STATIC_MAX_PARENTS
 lib.evaluate_gpu.restype = None
 lib.evaluate_gpu.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), Lb1BoundData,
                              Lb2BoundData, _vp, _vp, _vp, _vp]

@@ -223,6 +223,37 @@ int bb_pfsp_search(const bb_pfsp_instance *ins, int lb, int best0, int D, int ws
                    bb_search_result *res, bb_stats *per_gpu);
 int bb_nq_search(int N, int G, int D, int ws, const bb_config *cfg, bb_search_result *res, bb_stats *per_gpu);
 
+/* =====================================================================================================
+ * ALLOCATION-FREE STEP. This entry point has no counterpart in the reference.
+ *
+ * One bound -> prune -> branch step over a batch of parents (what bb_engine_push_nodes + bb_engine_run(1) +
+ * bb_engine_export_nodes do) for callers that must not allocate device memory while they work: host threads
+ * that share a GPU with other threads (cudaMalloc/cudaFree synchronise the device and would stall them all),
+ * hosts that have already given every free byte of HBM to their own pool, and code inside a stream capture or a
+ * latency-critical section where the runtime's allocator may not be entered. It calls no cudaMalloc, cudaFree or
+ * other allocating routine: its whole working set - control block, instance tables, both node stacks - is one
+ * file-scope __device__ array of about 4.6 MiB inside libbbgpu.so (present once on every GPU that loads the
+ * library, until the process exits).
+ *
+ *   ins         host instance tables (bb_pfsp_instance_*); lb: 0 = LB1_d, 1 = LB1 (LB2 is not offered here)
+ *   best        incumbent to prune against
+ *   parents_d   DEVICE pointer, `count` nodes in the reference layout; count <= BB_STATIC_MAX_PARENTS, larger
+ *               batches are refused with BB_ERR_ARG (split them)
+ *   children_d  DEVICE pointer, room for max_children nodes; survivors beyond max_children are dropped, so
+ *               compare result_d[0] with max_children (count * nb_jobs always suffices)
+ *   result_d    DEVICE pointer to 4 x unsigned long long: children produced, exploredTree increment,
+ *               exploredSol increment, incumbent after the step
+ *   stream      a cudaStream_t (NULL = default stream); work is only enqueued, the caller synchronises
+ *
+ * The array is shared by every call on that GPU and keeps what the last call left in it; each call clears the
+ * parts that must start at zero, but two calls whose GPU work can overlap race on it - keep them ordered.
+ * The first call on each device also resolves the array's device address and the launch geometry: make that
+ * call before any stream capture begins.
+ * ===================================================================================================== */
+#define BB_STATIC_MAX_PARENTS 2048
+int bb_pfsp_expand_static(const bb_pfsp_instance *ins, int lb, int best, const Node *parents_d, int count,
+                          Node *children_d, int max_children, unsigned long long *result_d, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
