@@ -11,6 +11,7 @@
 #include "bb_internal.cuh"
 #include "bb_nq_kernels.cuh"
 #include "bb_pfsp_kernels.cuh"
+#include "bb_pfsp_lb2.cuh"
 
 #include <climits>
 #include <cstdarg>
@@ -75,12 +76,14 @@ struct bb_engine
   bb_pfsp_dev T;
   void *table_mem;
   int lb, n, m, prefilter;
+  int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
   /* N-Queens */
   int N, G;
   /* launch */
   const void *kernel;
   int grid, smem;
+  int threads; /* per CTA */
   int iters_per_launch;
   cudaGraphExec_t graph;
   cudaEvent_t ev0, ev1, ev_begin, ev_end;
@@ -101,6 +104,8 @@ extern "C" void bb_config_default(bb_config *cfg)
   cfg->capacity = 0;
   cfg->iters_per_launch = 32;
   cfg->lb2_prefilter = 1;
+  cfg->lb2_staged = 1;
+  cfg->lb2_stage_a = 8;
 }
 
 /* ------------------------------------------------------------------ small kernels: plan / seed / export */
@@ -130,6 +135,26 @@ __global__ void k_reset(bb_ctrl *c, int best, int M, int capacity, int maxkids)
 }
 
 __global__ void k_set_best(bb_ctrl *c, int best) { atomicMin(&c->best, best); }
+
+/* LB2 staged kernel: forget the learned pair order (identity order, zero scores and histogram) */
+__global__ void k_lb2_reset_order(bb_pfsp_dev T)
+{
+  const int P = T.P;
+  for (int l = threadIdx.x; l < P; l += blockDim.x)
+  {
+    T.order[l] = l;
+    T.score[l] = 0u;
+    T.pairs_act[l] = T.pairs[l];
+  }
+  for (int l = threadIdx.x; l <= P; l += blockDim.x)
+    T.hist[l] = 0u;
+  for (int i = threadIdx.x; i < P * BB_MAX_JOBS; i += blockDim.x)
+  {
+    T.jbit_act[i] = T.jbit[i];
+    T.ja_act[i] = T.ja[i];
+    T.jb_act[i] = T.jb[i];
+  }
+}
 
 /* reference Node (int16 depth, limit1, prmu[20]) -> device record, deriving front/remain/mask
  * (schedule_front + sum_unscheduled of c_bound_simple.c:51-68, 108-124, done once per seeded node only) */
@@ -296,14 +321,15 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   return BB_OK;
 }
 
-static int setup_launch(bb_engine *e, const void *kernel, int smem)
+static int setup_launch(bb_engine *e, const void *kernel, int smem, int threads = BB_CTA_THREADS)
 {
   e->kernel = kernel;
   e->smem = smem;
+  e->threads = threads;
   if (smem > 48 * 1024)
     BB_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   int per_sm = 0, sms = 0;
-  BB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BB_CTA_THREADS, smem));
+  BB_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
   BB_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device));
   if (per_sm < 1)
     return bb_fail(BB_ERR_CUDA, "kernel does not fit on an SM (smem %d B)", smem);
@@ -315,13 +341,13 @@ static int launch_expand(bb_engine *e, cudaStream_t s)
 {
   if (e->kind == KIND_PFSP)
   {
-    void *args[] = {&e->ctrl, &e->pool, &e->T, &e->prefilter};
-    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(BB_CTA_THREADS), args, e->smem, s));
+    void *args[] = {&e->ctrl, &e->pool, &e->T, &e->prefilter, &e->stage_a};
+    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(e->threads), args, e->smem, s));
   }
   else
   {
     void *args[] = {&e->ctrl, &e->pool, &e->N, &e->G};
-    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(BB_CTA_THREADS), args, e->smem, s));
+    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(e->threads), args, e->smem, s));
   }
   return BB_OK;
 }
@@ -368,7 +394,10 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   const size_t sz_vec = ((size_t)m * 4 + 15) & ~(size_t)15;
   const size_t sz_slot = ((size_t)(P > 0 ? P : 1) * BB_MAX_JOBS * 4 + 15) & ~(size_t)15;
   const size_t sz_pairs = ((size_t)(P > 0 ? P : 1) * 8 + 15) & ~(size_t)15;
-  const size_t total = sz_p8 + 2 * sz_vec + 3 * sz_slot + sz_pairs;
+  const size_t sz_ord = ((size_t)((P > 0 ? P : 1) + 1) * 4 + 15) & ~(size_t)15;
+  const size_t canon = sz_p8 + 2 * sz_vec + 3 * sz_slot + sz_pairs;
+  /* + the learned-order copies of the four pair tables, order[], score[], hist[] (device-written) */
+  const size_t total = canon + 3 * sz_slot + sz_pairs + 3 * sz_ord;
   std::vector<unsigned char> h(total, 0);
   uint8_t *p8 = h.data();
   int *tails = (int *)(h.data() + sz_p8);
@@ -417,6 +446,13 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   e->T.ja = (const int *)(d + sz_p8 + 2 * sz_vec + sz_slot);
   e->T.jb = (const int *)(d + sz_p8 + 2 * sz_vec + 2 * sz_slot);
   e->T.pairs = (const int2 *)(d + sz_p8 + 2 * sz_vec + 3 * sz_slot);
+  e->T.jbit_act = (uint32_t *)(d + canon);
+  e->T.ja_act = (int *)(d + canon + sz_slot);
+  e->T.jb_act = (int *)(d + canon + 2 * sz_slot);
+  e->T.pairs_act = (int2 *)(d + canon + 3 * sz_slot);
+  e->T.order = (int *)(d + canon + 3 * sz_slot + sz_pairs);
+  e->T.score = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + sz_ord);
+  e->T.hist = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + 2 * sz_ord);
   e->T.best_known = ins->best_known;
   return BB_OK;
 }
@@ -428,6 +464,8 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
   e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
+  e->staged = (lb == 2) && (cfg ? (cfg->lb2_staged != 0) : 1) && ins->nb_machine_pairs > 0;
+  e->stage_a = cfg && cfg->lb2_stage_a > 0 ? cfg->lb2_stage_a : 8;
   int rc = alloc_common(e, cfg, bbk::pfsp_planes(e->m), 0);
   if (rc)
     return rc;
@@ -435,6 +473,17 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   if (rc)
     return rc;
   const int mm = bbk::pfsp_mm(e->m);
+  if (e->staged)
+  {
+    const void *k = mm == 5    ? (const void *)bbk::pfsp_expand_lb2<5>
+                    : mm == 10 ? (const void *)bbk::pfsp_expand_lb2<10>
+                    : mm == 20 ? (const void *)bbk::pfsp_expand_lb2<20>
+                               : (const void *)bbk::pfsp_expand_lb2<0>;
+    rc = setup_launch(e, k, bbk::lb2_layout(e->m, e->T.P).total, BB_LB2_THREADS);
+    if (rc)
+      return rc;
+    return build_graph(e);
+  }
   const void *k = lb == 0 ? pick_pfsp_kernel<0>(mm) : lb == 1 ? pick_pfsp_kernel<1>(mm) : pick_pfsp_kernel<2>(mm);
   const int smem = bbk::pfsp_layout(e->m, e->T.P, lb).total;
   rc = setup_launch(e, k, smem);
@@ -560,6 +609,8 @@ extern "C" int bb_engine_reset(bb_engine *e, int best)
     return bb_fail(BB_ERR_ARG, "null engine");
   ENGINE_SET_DEVICE(e);
   k_reset<<<1, 1, 0, e->stream>>>(e->ctrl, best, e->M, e->pool.capacity, e->kind == KIND_PFSP ? e->n : e->N);
+  if (e->kind == KIND_PFSP && e->staged)
+    k_lb2_reset_order<<<1, 256, 0, e->stream>>>(e->T); /* a new search learns its pair order from scratch */
   BB_CUDA_TRY(cudaGetLastError());
   e->kernel_ms = 0;
   e->span_ms = 0;
@@ -620,7 +671,7 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
                                                  e->pool.nplanes);
     else
       k_seed_nq<<<blocks, 128, 0, e->stream>>>((const uint8_t *)stage, count, e->pool, e->N, at);
-    k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, count, e->grid * BB_WARPS_PER_CTA);
+    k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, count, e->grid * (e->threads / 32));
     err = cudaGetLastError();
   }
   if (err == cudaSuccess)

@@ -45,6 +45,7 @@ struct __align__(256) bb_ctrl
   int tile;            /* parents per warp tile for this iteration */
   unsigned int tail;   /* append cursor of stack dst = 1 - src */
   unsigned int ticket; /* CTAs finished in this iteration */
+  unsigned int next_tile; /* dynamic tile hand-out of this iteration (staged LB2 kernel) */
   /* search state */
   int best;            /* incumbent upper bound (atomicMin) */
   int error;           /* sticky: 1 = pool overflow */
@@ -76,7 +77,16 @@ struct bb_pfsp_dev
   const uint32_t *jbit;  /* 1 << job */
   const int *ja;         /* p[m2][job] - p[m1][job] */
   const int *jb;         /* lag + p[m2][job] */
-  const int2 *pairs;     /* (m1, m2) in evaluation order */
+  const int2 *pairs;     /* (m1, m2) in the reference's evaluation order */
+  /* staged LB2 kernel: the same four tables in the LEARNED pair order (rewritten on the device between launches),
+   * the order itself, per-pair scores and the kill histogram by position (+1 slot: samples since the last sort) */
+  uint32_t *jbit_act;
+  int *ja_act;
+  int *jb_act;
+  int2 *pairs_act;
+  int *order;
+  unsigned *score;
+  unsigned *hist;
   int best_known;
 };
 

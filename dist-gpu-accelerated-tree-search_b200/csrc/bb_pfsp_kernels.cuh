@@ -147,13 +147,16 @@ __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
   int tile = (n + total_warps - 1) / total_warps;
   c->tile = tile < 1 ? 1 : (tile > BB_TILE_MAX ? BB_TILE_MAX : tile);
   c->ticket = 0;
+  c->next_tile = 0;
 }
 
 /* counters accumulated per thread, reduced per warp -> CTA -> one global atomic each; then the last CTA to
  * finish commits the stack sizes and plans the next iteration. */
-__device__ __forceinline__ void finish_iteration(bb_ctrl *ctrl, unsigned long long (&cnt)[6], int src, int base,
+/* returns true in thread 0 of the last CTA to finish, false everywhere else */
+__device__ __forceinline__ bool finish_iteration(bb_ctrl *ctrl, unsigned long long (&cnt)[6], int src, int base,
                                                  int cap)
 {
+  bool last = false;
   __shared__ unsigned long long cta_cnt[6];
   const int lane = threadIdx.x & 31;
   if (threadIdx.x < 6)
@@ -183,9 +186,11 @@ __device__ __forceinline__ void finish_iteration(bb_ctrl *ctrl, unsigned long lo
       ctrl->size[src] = base;
       ctrl->size[1 - src] = (int)tl;
       ctrl->iterations += 1;
-      plan_next(ctrl, 1 - src, gridDim.x * BB_WARPS_PER_CTA);
+      plan_next(ctrl, 1 - src, gridDim.x * (blockDim.x >> 5));
+      last = true;
     }
   }
+  return last;
 }
 
 template <int LB, int MM>

@@ -162,6 +162,9 @@ typedef struct bb_config
   long long capacity;     /* nodes per stack (two stacks are allocated); <=0: chosen from M */
   int iters_per_launch;   /* device iterations chained in one CUDA-graph launch; <=0: 32 */
   int lb2_prefilter;      /* LB2 only: 1 = skip the pair loop for children LB1_d already prunes (default 1) */
+  int lb2_staged;         /* LB2 only: 1 = staged kernel with learned pair order and candidate compaction (default),
+                             0 = first-generation kernel walking the pairs in the reference's order */
+  int lb2_stage_a;        /* LB2 staged kernel: pairs tried before the survivors are compacted; <=0: 8 */
 } bb_config;
 
 typedef struct bb_stats
