@@ -68,7 +68,25 @@ class Stats(C.Structure):
 
 class SearchResult(C.Structure):
     _fields_ = [("tree", C.c_ulonglong), ("sol", C.c_ulonglong), ("best", C.c_int), ("elapsed_s", C.c_double),
-                ("kernel_ms_max", C.c_double), ("steals", C.c_ulonglong), ("steals_ok", C.c_ulonglong)]
+                ("kernel_ms_max", C.c_double), ("steals", C.c_ulonglong), ("steals_ok", C.c_ulonglong),
+                ("search_s", C.c_double), ("nodes_moved", C.c_ulonglong)]
+
+
+class TeamResult(C.Structure):
+    _fields_ = [("best", C.c_int), ("steals", C.c_ulonglong), ("steals_ok", C.c_ulonglong),
+                ("donated", C.c_ulonglong), ("busy_ms", C.c_double)]
+
+
+class TeamOps(C.Structure):  # bb_team_ops: how the team protocol reaches a worker's engine
+    RUN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_longlong, C.POINTER(C.c_longlong), C.POINTER(C.c_int),
+                      C.POINTER(C.c_double))
+    DONATE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_longlong, C.c_longlong, C.POINTER(C.c_int),
+                         C.POINTER(C.c_longlong), C.POINTER(C.c_longlong))
+    DONE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)
+    PULL = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_longlong)
+    SETBEST = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)
+    _fields_ = [("self", C.c_void_p), ("run", RUN), ("donate", DONATE), ("donate_done", DONE), ("pull", PULL),
+                ("set_best", SETBEST)]
 
 
 _i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -82,7 +100,9 @@ EXPORTS = [
     "bb_pfsp_instance_taillard", "bb_pfsp_instance_from_ptimes", "bb_pfsp_instance_free", "bb_config_default",
     "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_engine_reset", "bb_engine_push_root",
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
-    "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static",
+    "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist",
+    "bb_team_bytes", "bb_team_init", "bb_team_wait_ready", "bb_team_barrier", "bb_team_fail", "bb_team_worker",
+    "bb_team_best",
 ]
 
 lib.bb_last_error.restype = C.c_char_p
@@ -111,6 +131,20 @@ lib.bb_pfsp_search.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, C.c_in
                                C.POINTER(SearchResult), C.POINTER(Stats)]
 lib.bb_nq_search.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(Config), C.POINTER(SearchResult),
                              C.POINTER(Stats)]
+lib.bb_pfsp_search_dist.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int,
+                                    C.POINTER(Config), C.POINTER(SearchResult), C.POINTER(Stats)]
+lib.bb_nq_search_dist.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(Config),
+                                  C.POINTER(SearchResult), C.POINTER(Stats)]
+lib.bb_team_bytes.restype = C.c_size_t
+lib.bb_team_bytes.argtypes = [C.c_int]
+lib.bb_team_init.argtypes = [_vp, C.c_int]
+lib.bb_team_wait_ready.argtypes = [_vp, C.c_int, C.c_double]
+lib.bb_team_barrier.argtypes = [_vp, C.c_double]
+lib.bb_team_fail.restype = None
+lib.bb_team_fail.argtypes = [_vp]
+lib.bb_team_worker.argtypes = [_vp, C.c_int, C.POINTER(TeamOps), C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.c_int,
+                               C.POINTER(TeamResult)]
+lib.bb_team_best.argtypes = [_vp]
 lib.bb_pfsp_expand_static.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp]
 STATIC_MAX_PARENTS = 2048  # BB_STATIC_MAX_PARENTS
 lib.evaluate_gpu.restype = None
@@ -244,6 +278,21 @@ def pfsp_search(instance, lb, best0=None, D=1, ws=1, **cfg):
     check(lib.bb_pfsp_search(instance.ptr, lb, best0, D, ws, C.byref(default_config(**cfg)), C.byref(res), per),
           "bb_pfsp_search")
     return res, list(per)
+
+
+def pfsp_search_dist(instance, lb, rank, world, shm_name, best0=None, ws=1, **cfg):
+    res, mine = SearchResult(), Stats()
+    best0 = instance.best_known if best0 is None else best0
+    check(lib.bb_pfsp_search_dist(instance.ptr, lb, best0, rank, world, shm_name.encode(), ws,
+                                  C.byref(default_config(**cfg)), C.byref(res), C.byref(mine)), "bb_pfsp_search_dist")
+    return res, mine
+
+
+def nq_search_dist(N, G, rank, world, shm_name, ws=1, **cfg):
+    res, mine = SearchResult(), Stats()
+    check(lib.bb_nq_search_dist(N, G, rank, world, shm_name.encode(), ws, C.byref(default_config(**cfg)),
+                                C.byref(res), C.byref(mine)), "bb_nq_search_dist")
+    return res, mine
 
 
 def nq_search(N, G=1, D=1, ws=1, **cfg):

@@ -207,13 +207,13 @@ __global__ void k_seed_pfsp(const int16_t *__restrict__ nodes, int count, bb_poo
     pool.planes[0][(size_t)q * pool.capacity + at + i] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
 }
 
-__global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int stack, int count, int out_at)
+__global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int stack, int from, int count, int out_at)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
-  const uint4 q0 = pool.planes[stack][i];
-  const uint4 q1 = pool.planes[stack][(size_t)pool.capacity + i];
+  const uint4 q0 = pool.planes[stack][from + i];
+  const uint4 q1 = pool.planes[stack][(size_t)pool.capacity + from + i];
   const uint32_t w[6] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y};
   int16_t *nd = nodes + (size_t)(out_at + i) * (2 + BB_MAX_JOBS);
   const int depth = w[5] & 0xff;
@@ -247,15 +247,16 @@ __global__ void k_seed_nq(const uint8_t *__restrict__ nodes, int count, bb_pool 
     pool.tailw[0][(size_t)(at + i) * pool.tail_words + t] = ww[4 + t];
 }
 
-__global__ void k_export_nq(uint8_t *__restrict__ nodes, bb_pool pool, int stack, int count, int out_at, int N)
+__global__ void k_export_nq(uint8_t *__restrict__ nodes, bb_pool pool, int stack, int from, int count, int out_at,
+                            int N)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
-  const uint4 q0 = pool.planes[stack][i];
+  const uint4 q0 = pool.planes[stack][from + i];
   uint32_t ww[6] = {q0.x, q0.y, q0.z, q0.w, 0u, 0u};
   for (int t = 0; t < pool.tail_words; t++)
-    ww[4 + t] = pool.tailw[stack][(size_t)i * pool.tail_words + t];
+    ww[4 + t] = pool.tailw[stack][(size_t)(from + i) * pool.tail_words + t];
   uint8_t *nd = nodes + (size_t)(out_at + i) * (1 + BB_MAX_QUEENS);
   const int db = N <= 15 ? 15 : N;
   nd[0] = (uint8_t)((ww[db >> 2] >> (8 * (db & 3))) & 0xff);
@@ -712,7 +713,7 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
   int rc = fetch_ctrl(e);
   if (rc)
     return rc;
-  const long long total = (long long)e->ctrl_h->size[0] + e->ctrl_h->size[1];
+  const long long total = (long long)(e->ctrl_h->size[0] - e->ctrl_h->bot[0]) + (e->ctrl_h->size[1] - e->ctrl_h->bot[1]);
   if (total > max_count)
     return bb_fail(BB_ERR_ARG, "export buffer holds %lld nodes, pool has %lld", max_count, total);
   if (total == 0)
@@ -723,14 +724,14 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
   int at = 0;
   for (int s = 0; s < 2; s++)
   {
-    const int cnt = e->ctrl_h->size[s];
+    const int from = e->ctrl_h->bot[s], cnt = e->ctrl_h->size[s] - from;
     if (!cnt)
       continue;
     const int blocks = (cnt + 127) / 128;
     if (e->kind == KIND_PFSP)
-      k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, cnt, at);
+      k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else
-      k_export_nq<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, cnt, at, e->N);
+      k_export_nq<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, from, cnt, at, e->N);
     at += cnt;
   }
   cudaError_t err = cudaGetLastError();
@@ -755,7 +756,7 @@ static void fill_stats(bb_engine *e, bb_stats *out)
   out->lb2_pairs = c->lb2_pairs;
   out->iterations = c->iterations;
   out->launches = e->launches;
-  out->pool_size = (long long)c->size[0] + c->size[1];
+  out->pool_size = (long long)(c->size[0] - c->bot[0]) + (c->size[1] - c->bot[1]);
   out->max_pool = c->max_pool;
   out->best = c->best;
   out->kernel_ms = e->kernel_ms;
@@ -779,6 +780,119 @@ extern "C" int bb_engine_get_stats(bb_engine *e, bb_stats *out)
   fill_stats(e, out);
   return BB_OK;
 }
+
+/* ------------------------------------------------------------------ sharing work between GPUs (bb_multi.cu)
+ * Replaces the host-memory steal of the reference (popBackBulkFree(victim, m, 5M, stolen, 2) + pushBackBulk,
+ * pfsp_multigpu_cuda.c:355-404): the victim only RESERVES the oldest nodes of one of its stacks (they sit at the
+ * bottom: shallow nodes, large sub-trees); the thief copies the planes straight out of the victim's HBM over
+ * NVLink (peer access in one process, CUDA IPC between processes) and appends them to its own stack. */
+
+__global__ void k_donate(bb_ctrl *c, int stack, int count, int total_warps)
+{
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+  {
+    c->bot[stack] += count;
+    c->hold[stack] += 1;
+    bbk::plan_next(c, c->src, total_warps); /* the planned batch may have reached into the donated range */
+  }
+}
+
+__global__ void k_donate_done(bb_ctrl *c, int stack, int total_warps)
+{
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+  {
+    c->hold[stack] -= 1;
+    bbk::plan_next(c, c->src, total_warps);
+  }
+}
+
+int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int *stack, long long *start,
+                     long long *count)
+{
+  *count = 0;
+  ENGINE_SET_DEVICE(e);
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  const bb_ctrl *c = e->ctrl_h;
+  const long long a0 = c->size[0] - c->bot[0], a1 = c->size[1] - c->bot[1];
+  if (c->error || a0 + a1 < 2 * min_keep || a0 + a1 < 2)
+    return BB_OK;
+  const int s = a0 >= a1 ? 0 : 1;
+  long long give = (a0 + a1) / 2;
+  if (give > (s == 0 ? a0 : a1))
+    give = s == 0 ? a0 : a1;
+  if (give > max_count)
+    give = max_count;
+  if (give <= 0)
+    return BB_OK;
+  *stack = s;
+  *start = c->bot[s];
+  *count = give;
+  k_donate<<<1, 1, 0, e->stream>>>(e->ctrl, s, (int)give, e->grid * (e->threads / 32));
+  BB_CUDA_TRY(cudaGetLastError());
+  return fetch_ctrl(e);
+}
+
+int bb_engine_donate_done(bb_engine *e, int stack)
+{
+  ENGINE_SET_DEVICE(e);
+  k_donate_done<<<1, 1, 0, e->stream>>>(e->ctrl, stack, e->grid * (e->threads / 32));
+  BB_CUDA_TRY(cudaGetLastError());
+  return fetch_ctrl(e);
+}
+
+/* thief side: copy `count` records starting at `start` out of a peer's stack (plane base, tail-word base and
+ * capacity of THAT stack, device pointers valid on this device) onto the top of our stack 0 */
+int bb_engine_pull(bb_engine *e, const void *peer_planes, const void *peer_tailw, long long peer_capacity,
+                   long long start, long long count)
+{
+  ENGINE_SET_DEVICE(e);
+  int rc = fetch_ctrl(e);
+  if (rc)
+    return rc;
+  const long long at = e->ctrl_h->size[0];
+  if (at + count > e->pool.capacity)
+    return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while taking over %lld nodes", e->pool.capacity, count);
+  BB_CUDA_TRY(cudaMemcpy2DAsync(e->pool.planes[0] + at, (size_t)e->pool.capacity * sizeof(uint4),
+                                (const uint4 *)peer_planes + start, (size_t)peer_capacity * sizeof(uint4),
+                                (size_t)count * sizeof(uint4), e->pool.nplanes, cudaMemcpyDeviceToDevice, e->stream));
+  if (e->pool.tail_words)
+    BB_CUDA_TRY(cudaMemcpyAsync(e->pool.tailw[0] + at * e->pool.tail_words,
+                                (const uint32_t *)peer_tailw + start * e->pool.tail_words,
+                                (size_t)count * e->pool.tail_words * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
+                                e->stream));
+  k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, (int)count, e->grid * (e->threads / 32));
+  BB_CUDA_TRY(cudaGetLastError());
+  return fetch_ctrl(e);
+}
+
+void bb_engine_pool_info(bb_engine *e, void **planes, void **tailw, long long *capacity, int *device)
+{
+  for (int s = 0; s < 2; s++)
+  {
+    planes[s] = e->pool.planes[s];
+    tailw[s] = e->pool.tailw[s];
+  }
+  *capacity = e->pool.capacity;
+  *device = e->device;
+}
+
+/* zero the search counters but keep the pool (workers other than 0 after the common warm-up) */
+__global__ void k_zero_counters(bb_ctrl *c)
+{
+  c->tree = c->sol = c->parents = c->evals = c->lb2_evals = c->lb2_pairs = c->iterations = 0ull;
+}
+
+int bb_engine_zero_counters(bb_engine *e)
+{
+  ENGINE_SET_DEVICE(e);
+  k_zero_counters<<<1, 1, 0, e->stream>>>(e->ctrl);
+  BB_CUDA_TRY(cudaGetLastError());
+  return fetch_ctrl(e);
+}
+
+int bb_engine_kind_is_pfsp(const bb_engine *e) { return e->kind == KIND_PFSP; }
 
 /* ------------------------------------------------------------------ the device loop */
 

@@ -116,11 +116,16 @@ __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb)
  * cannot fill a batch and the other one is larger. */
 __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
 {
-  const int total = c->size[0] + c->size[1];
+  /* a drained stack rewinds to index 0 unless a peer is still copying a donated chunk out of it */
+  for (int s = 0; s < 2; s++)
+    if (c->size[s] == c->bot[s] && c->hold[s] == 0)
+      c->size[s] = c->bot[s] = 0;
+  const int avail[2] = {c->size[0] - c->bot[0], c->size[1] - c->bot[1]};
+  const int total = avail[0] + avail[1];
   if (total > c->max_pool)
     c->max_pool = total;
   int src = preferred;
-  const int sp = c->size[preferred], so = c->size[1 - preferred];
+  const int sp = avail[preferred], so = avail[1 - preferred];
   if (!(sp >= c->M || sp >= so))
     src = 1 - preferred;
   /* never pop more parents than the destination stack can take children of (capacity guard): the batch shrinks
@@ -129,10 +134,10 @@ __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
   for (int attempt = 0; attempt < 2; attempt++)
   {
     const int room = (c->capacity - c->size[1 - src]) / c->maxkids;
-    n = c->size[src] < c->M ? c->size[src] : c->M;
+    n = avail[src] < c->M ? avail[src] : c->M;
     if (n > room)
       n = room;
-    if (n > 0 || c->size[1 - src] == 0)
+    if (n > 0 || avail[1 - src] == 0)
       break;
     src = 1 - src;
   }

@@ -217,14 +217,60 @@ typedef struct bb_search_result
   unsigned long long tree;
   unsigned long long sol;
   int best;
-  double elapsed_s;     /* wall time of the whole search */
+  double elapsed_s;     /* wall time of the whole call (engine creation, table upload, search, teardown) */
   double kernel_ms_max; /* max over GPUs of device time in expand kernels */
   unsigned long long steals, steals_ok;
+  double search_s;      /* max over GPUs of the wall time from the common start barrier (pools seeded, tables
+                           resident) to the detection of global termination */
+  unsigned long long nodes_moved; /* nodes that changed GPU through work stealing */
 } bb_search_result;
 
 int bb_pfsp_search(const bb_pfsp_instance *ins, int lb, int best0, int D, int ws, const bb_config *cfg,
                    bb_search_result *res, bb_stats *per_gpu);
 int bb_nq_search(int N, int G, int D, int ws, const bb_config *cfg, bb_search_result *res, bb_stats *per_gpu);
+
+/* The same searches with one PROCESS per GPU (rank = 0..world-1 on one node, e.g. under torchrun): every rank calls
+ * with the same arguments and its own cfg->device; ranks meet in the POSIX shared-memory object `shm_name`
+ * (created by whoever arrives first, unlinked by rank 0 at the end; use a fresh name per call), exchange CUDA IPC
+ * handles of their pools through it and steal from each other's HBM over NVLink. Every rank returns the global
+ * totals in `res`; `mine` (may be NULL) gets the caller's own engine statistics. */
+int bb_pfsp_search_dist(const bb_pfsp_instance *ins, int lb, int best0, int rank, int world, const char *shm_name,
+                        int ws, const bb_config *cfg, bb_search_result *res, bb_stats *mine);
+int bb_nq_search_dist(int N, int G, int rank, int world, const char *shm_name, int ws, const bb_config *cfg,
+                      bb_search_result *res, bb_stats *mine);
+
+/* ----- the team protocol underneath (host code only; replaces the steal loop pfsp_multigpu_cuda.c:343-404, the
+ * allIdle termination common/util.c:19-38 and checkBest pfsp_multigpu_cuda.c:30-50). `mem` is a zero-filled block
+ * of bb_team_bytes(world) bytes visible to every worker (heap for threads, a shared mapping for processes).
+ * A worker reaches its engine only through bb_team_ops. */
+typedef struct bb_team_ops
+{
+  void *self;
+  /* run at most max_iters pool iterations; report nodes left, the incumbent and device time spent */
+  int (*run)(void *self, long long max_iters, long long *pool_size, int *best, double *busy_ms);
+  /* reserve the oldest nodes of one stack for a thief: count = 0 when fewer than 2*min_keep nodes are left */
+  int (*donate)(void *self, long long min_keep, long long max_count, int *stack, long long *start, long long *count);
+  int (*donate_done)(void *self, int stack); /* the thief has copied the range out */
+  /* thief side: copy [start, start+count) of `stack` out of worker `victim`'s memory into the own pool */
+  int (*pull)(void *self, int victim, int stack, long long start, long long count);
+  int (*set_best)(void *self, int best);
+} bb_team_ops;
+
+typedef struct bb_team_result
+{
+  int best;
+  unsigned long long steals, steals_ok, donated;
+  double busy_ms;
+} bb_team_result;
+
+size_t bb_team_bytes(int world);
+int bb_team_init(void *mem, int world);                          /* by one worker, before the others use mem */
+int bb_team_wait_ready(void *mem, int world, double timeout_s);  /* by the others */
+int bb_team_barrier(void *mem, double timeout_s);
+void bb_team_fail(void *mem);
+int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws, long long m_keep, long long max_steal,
+                   int best0, int iters_per_poll, bb_team_result *out);
+int bb_team_best(void *mem);
 
 /* =====================================================================================================
  * ALLOCATION-FREE STEP. This entry point has no counterpart in the reference.

@@ -20,6 +20,7 @@ def fnv_hex(a):
 def declared_functions():
     src = open(os.path.join(ROOT, "include", "bb_gpu.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = re.sub(r"\{[^{}]*\}", "{}", src)  # struct / enum bodies (function-pointer members are not exports)
     names = re.findall(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\([^;{}]*\)\s*;", src)
     return sorted(set(n for n in names if not n.startswith("defined")))
 
