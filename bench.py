@@ -169,35 +169,51 @@ def run_reference_arm(args, w, rank):
 
 # ------------------------------------------------------------------ our arm
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=3)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="pfsp:21:2")
-    ap.add_argument("--M", type=int, default=1 << 20, help="max parents per device iteration (-M)")
-    ap.add_argument("--ref-seconds", type=float, default=12.0)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
-    w = parse_workload(args.workload)
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+def ncu_traffic(kernel_key):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/), or None"""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p)).get(kernel_key)
+    return None
 
-    if args.impl == "reference":
-        run_reference_arm(args, w, rank)
-        return
 
-    import torch
-    from __graft_entry__ import load_package
-    bb = load_package()  # raises if libbbgpu.so is missing: there is no fallback path
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
-    torch.cuda.set_device(local_rank)
-    if world > 1:
-        raise SystemExit("multi-process runs are handled by bench_multi (not built yet)")
+def kernel_key(w):
+    if w[0] == "nq":
+        return "nq_expand"
+    return {0: "pfsp_expand_lb1d", 1: "pfsp_expand_lb1", 2: "pfsp_expand_lb2"}[w[2]]
 
+
+def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters, lb2_pairs, device):
+    """HBM roofline of the expand kernel (algorithmic bytes: every explored node is written once as a survivor and
+    read once as a parent); for LB2 additionally the integer-pipe roofline in LB2 slot steps."""
+    peak, peak_src = measured_peaks()
+    alg_bytes = (parents + nodes) * rec_alg
+    achieved = alg_bytes / (kernel_ms / 1e3) / 1e9
+    tr = ncu_traffic(kernel_key(w))
+    roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": tr["dram_bytes_per_launch"] if tr else None,
+            "traffic_note": tr["note"] if tr else None, "peak_source": peak_src,
+            "kernel": {"nq_expand": "bbk::nq_expand", "pfsp_expand_lb2": "bbk::pfsp_expand_lb2"}.get(
+                kernel_key(w), "bbk::pfsp_expand"),
+            "algorithmic_bytes_per_node": 2 * rec_alg, "record_bytes_in_pool": rec_pool,
+            "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1)}
+    extra = {}
+    if w[0] == "pfsp" and w[2] == 2:
+        pk = C.c_double(0)
+        bb.check(bb.lib.bb_measure_slot_step_peak(device, C.byref(pk)), "bb_measure_slot_step_peak")
+        steps = lb2_pairs * 20  # each evaluated (child, pair) walks the 20 Johnson slots: one bit test + one add-max
+        ach = steps / (kernel_ms / 1e3)
+        roof["note"] = ("LB2 is bound by the integer ALU pipe, not HBM (ncu: ALU pipe ~69 % busy, DRAM < 2 %); the "
+                        "binding roofline is roofline_int below")
+        extra["roofline_int"] = {"bound": "int_alu", "achieved": ach / 1e9, "peak": pk.value / 1e9,
+                                 "unit": "G slot-steps/s", "frac": ach / pk.value,
+                                 "peak_source": "measured in this run (bb_measure_slot_step_peak: LOP3 test + "
+                                                "predicated VIADDMNMX only, all SMs)",
+                                 "slot_steps_per_pair": 20}
+    return roof, extra
+
+
+def run_single(args, w, bb, torch, local_rank):
     K, W = args.steps, max(args.warmup, 0)
     if w[0] == "pfsp":
         ins = bb.Instance(inst=w[1])
@@ -205,6 +221,7 @@ def main():
         best0 = ins.best_known
         rec_alg = ins.n + 2 + 4 * ins.m  # prmu + depth (+pad) + cached front/remain uint16[m] each
     else:
+        ins = None
         eng = bb.Engine.nqueens(w[1], 1, device=local_rank, M=args.M)
         best0 = bb.INT_MAX
         rec_alg = w[1] + 1
@@ -254,9 +271,8 @@ def main():
         e2e_h2d = per[0].h2d_bytes + per[0].table_bytes
         e2e_d2h = per[0].d2h_bytes
 
-    peak, peak_src = measured_peaks()
-    alg_bytes = (parents + nodes) * rec_alg  # every explored node is written once and read once
-    achieved = alg_bytes / (kernel_ms / 1e3) / 1e9
+    roof, extra = roofline_objects(bb, w, rec_alg, st.record_bytes, parents, nodes, kernel_ms, iters, lb2_pairs,
+                                   local_rank)
     line = {
         "metric": "explored_nodes_per_sec", "value": value, "unit": "nodes/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": span_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -264,17 +280,16 @@ def main():
         "config": {"workload": workload_name(w), "M": args.M, "tree_nodes": st.tree, "solutions": st.sol,
                    "optimum": st.best if w[0] == "pfsp" else None,
                    "l2": "no flush needed: each step streams the node pool through HBM, far more than the 126 MB L2",
+                   "timing": "CUDA events on the engine's launching stream, first to last launch of each step",
                    "time_to_optimum_s": span_ms / K / 1e3, "wall_s_per_step": wall / K,
                    "device_iterations_per_step": iters // K, "grid": st.grid, "smem_bytes": st.smem_bytes},
         "clocks": clocks,
         "e2e": {"value": e2e_nodes / e2e_t, "unit": "nodes/s", "h2d_bytes_per_step": int(e2e_h2d),
                 "d2h_bytes_per_step": int(e2e_d2h)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "kernel": "bbk::pfsp_expand" if w[0] == "pfsp" else "bbk::nq_expand",
-                     "algorithmic_bytes_per_node": 2 * rec_alg, "record_bytes_in_pool": st.record_bytes,
-                     "avg_launch_us": kernel_ms * 1e3 / max(iters, 1)},
+        "roofline": roof,
     }
+    line.update(extra)
     if w[0] == "pfsp" and w[2] == 2:
         line["lb2"] = {"child_bounds": evals // K, "pair_loops": lb2_evals // K, "pairs_evaluated": lb2_pairs // K,
                        "pairs_per_loop": lb2_pairs / max(lb2_evals, 1),
@@ -282,6 +297,130 @@ def main():
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_reference(w, args.ref_seconds)
     print(json.dumps(line), flush=True)
+
+
+def run_multi(args, w, bb, torch, rank, world, local_rank):
+    """one rank per GPU (torchrun): bb_*_search_dist - every step is a whole search shared by all ranks (strong
+    scaling): common warm-up, hash partition, peer-memory work stealing over NVLink, termination detection"""
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    K, W = args.steps, max(args.warmup, 0)
+    ins = bb.Instance(inst=w[1]) if w[0] == "pfsp" else None
+    rec_alg = (ins.n + 2 + 4 * ins.m) if ins else w[1] + 1
+    tag = [f"/bbgpu_{os.getpid()}_{int(time.time() * 1e3) & 0xffffff}"]
+    dist.broadcast_object_list(tag, src=0)
+
+    def one_step(i):
+        name = f"{tag[0]}_{i}"
+        if w[0] == "pfsp":
+            return bb.pfsp_search_dist(ins, w[2], rank, world, name, device=local_rank, M=args.M)
+        return bb.nq_search_dist(w[1], 1, rank, world, name, device=local_rank, M=args.M)
+
+    for i in range(W):
+        res, mine = one_step(i)
+    dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    search_s = call_s = 0.0
+    acc = dict(nodes=0, launches=0, parents=0, iters=0, lb2_pairs=0, lb2_evals=0, evals=0, kernel_ms=0.0, h2d=0,
+               d2h=0, steals=0, moved=0)
+    t_all = time.perf_counter()
+    for i in range(K):
+        t = time.perf_counter()
+        res, mine = one_step(W + i)
+        dt = time.perf_counter() - t
+        search_s += res.search_s  # already the max over ranks (computed inside the library from every rank's span)
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        call_s += float(tt.item())
+        acc["nodes"] += res.tree
+        acc["steals"] += res.steals_ok
+        acc["moved"] += res.nodes_moved
+        loc = torch.tensor([mine.launches + 6, mine.parents, mine.iterations, mine.lb2_pairs, mine.lb2_evals,
+                            mine.evals, mine.h2d_bytes + mine.table_bytes, mine.d2h_bytes], dtype=torch.int64,
+                           device="cuda")
+        dist.all_reduce(loc)
+        for k, v in zip(("launches", "parents", "iters", "lb2_pairs", "lb2_evals", "evals", "h2d", "d2h"), loc.tolist()):
+            acc[k] += v
+        km = torch.tensor([mine.kernel_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(km)
+        acc["kernel_ms"] += float(km.item())  # sum over ranks: GPU-time spent in expand kernels
+    dist.barrier()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t_all
+    clocks = sampler.stop() if sampler else None
+    exp = KNOWN_TREES.get(w)
+    if exp is not None and res.tree != exp:
+        raise SystemExit(f"PARITY FAILURE: explored tree {res.tree} != reference {exp}")
+    if rank == 0:
+        # per-kernel roofline: all ranks' algorithmic bytes over all ranks' kernel time = the average GPU's rate
+        roof, extra = roofline_objects(bb, w, rec_alg, mine.record_bytes, acc["parents"], acc["nodes"],
+                                       acc["kernel_ms"], acc["iters"], acc["lb2_pairs"], local_rank)
+        roof["note_multi"] = "per-GPU average: bytes of all ranks / expand-kernel time summed over ranks"
+        line = {
+            "metric": "explored_nodes_per_sec", "value": acc["nodes"] / search_s, "unit": "nodes/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": search_s / K * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "int32",
+            "data": "synthetic (Taillard LCG instance / root board generated in-process)",
+            "config": {"workload": workload_name(w), "M": args.M, "tree_nodes": res.tree, "solutions": res.sol,
+                       "optimum": res.best if w[0] == "pfsp" else None,
+                       "parallelism": f"search-tree partition over {world} GPUs: hash split of the warm-up pool + "
+                                      "peer-memory work stealing (CUDA IPC over NVLink), no data-path collective",
+                       "l2": "no flush needed: each step streams the node pool through HBM, far more than the 126 MB L2",
+                       "timing": "per step: max over ranks of the span from the common start barrier (pools seeded, "
+                                 "tables resident) to global termination, taken inside the library on every rank",
+                       "time_to_optimum_s": search_s / K, "wall_s_per_step": wall / K,
+                       "steals_per_step": acc["steals"] / K, "nodes_moved_per_step": acc["moved"] / K,
+                       "device_iterations_per_step": acc["iters"] // K, "grid": mine.grid,
+                       "smem_bytes": mine.smem_bytes},
+            "clocks": clocks,
+            "e2e": {"value": acc["nodes"] / call_s, "unit": "nodes/s", "h2d_bytes_per_step": int(acc["h2d"] // K),
+                    "d2h_bytes_per_step": int(acc["d2h"] // K),
+                    "note": "the bb_*_search_dist call itself with host tables: engine creation, pool cudaMalloc, "
+                            "table upload, IPC exchange, search, teardown; max over ranks"},
+            "gpu_launches": int(acc["launches"]),
+            "roofline": roof,
+        }
+        line.update(extra)
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = None  # measured at N=1 only (bench contract)
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="pfsp:21:2")
+    ap.add_argument("--M", type=int, default=1 << 20, help="max parents per device iteration (-M)")
+    ap.add_argument("--ref-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    w = parse_workload(args.workload)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, w, rank)
+        return
+
+    import torch
+    from __graft_entry__ import load_package
+    bb = load_package()  # raises if libbbgpu.so is missing: there is no fallback path
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        run_multi(args, w, bb, torch, rank, world, local_rank)
+    else:
+        run_single(args, w, bb, torch, local_rank)
 
 
 if __name__ == "__main__":

@@ -102,7 +102,7 @@ EXPORTS = [
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
     "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist",
     "bb_team_bytes", "bb_team_init", "bb_team_wait_ready", "bb_team_barrier", "bb_team_fail", "bb_team_worker",
-    "bb_team_best",
+    "bb_team_best", "bb_measure_slot_step_peak",
 ]
 
 lib.bb_last_error.restype = C.c_char_p
@@ -145,6 +145,7 @@ lib.bb_team_fail.argtypes = [_vp]
 lib.bb_team_worker.argtypes = [_vp, C.c_int, C.POINTER(TeamOps), C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.c_int,
                                C.POINTER(TeamResult)]
 lib.bb_team_best.argtypes = [_vp]
+lib.bb_measure_slot_step_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
 lib.bb_pfsp_expand_static.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp]
 STATIC_MAX_PARENTS = 2048  # BB_STATIC_MAX_PARENTS
 lib.evaluate_gpu.restype = None

@@ -52,6 +52,29 @@ double now_s()
   return duration<double>(steady_clock::now().time_since_epoch()).count();
 }
 
+/* span of the parallel phase on the device timeline: two events on the (idle) default stream of the current
+ * device bracket bb_team_worker; the engine's own stream is non-blocking, so they do not serialise with it */
+struct device_span
+{
+  cudaEvent_t a = nullptr, b = nullptr;
+  void begin()
+  {
+    if (cudaEventCreate(&a) == cudaSuccess && cudaEventCreate(&b) == cudaSuccess)
+      cudaEventRecord(a, 0);
+  }
+  double end_s(double fallback)
+  {
+    float ms = -1.f;
+    if (a && b && cudaEventRecord(b, 0) == cudaSuccess && cudaEventSynchronize(b) == cudaSuccess)
+      cudaEventElapsedTime(&ms, a, b);
+    if (a)
+      cudaEventDestroy(a);
+    if (b)
+      cudaEventDestroy(b);
+    return ms >= 0.f ? ms * 1e-3 : fallback;
+  }
+};
+
 struct peer_view
 {
   void *planes[2];
@@ -301,9 +324,13 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       if (bb_team_barrier(team, 120) == BB_OK && !o.rc)
       {
         const double s0 = now_s();
+        cudaSetDevice(i);
+        device_span span;
+        span.begin();
         bb_team_ops ops = gpu_ops(&w);
         rc = bb_team_worker(team, i, &ops, ws, m_keep, 5 * M, best, c.iters_per_launch, &o.tr);
-        o.search_s = now_s() - s0;
+        cudaSetDevice(i);
+        o.search_s = span.end_s(now_s() - s0);
         if (rc)
           fail(rc);
         else
@@ -466,9 +493,13 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   if (!rc)
   {
     const double s0 = now_s();
+    cudaSetDevice(c.device);
+    device_span span;
+    span.begin();
     bb_team_ops ops = gpu_ops(&w);
     const int r2 = bb_team_worker(mem, rank, &ops, ws, m_keep, 5 * M, best, c.iters_per_launch, &tr);
-    search_s = now_s() - s0;
+    cudaSetDevice(c.device);
+    search_s = span.end_s(now_s() - s0);
     if (r2)
       fail(r2);
     else

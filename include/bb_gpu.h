@@ -272,6 +272,11 @@ int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws, long long 
                    int best0, int iters_per_poll, bb_team_result *out);
 int bb_team_best(void *mem);
 
+/* Measured ceiling for the LB2 roofline (SURVEY section 8(d) asks for a measured integer-pipe peak; the reference's own
+ * op model is PFSP_gpu_lib.cu:244-254): sustained rate of the LB2 inner step - one job-bit test plus one predicated
+ * fused add-max per lane - on `device`, in slot steps per second. */
+int bb_measure_slot_step_peak(int device, double *slot_steps_per_s);
+
 /* =====================================================================================================
  * ALLOCATION-FREE STEP. This entry point has no counterpart in the reference.
  *
