@@ -76,6 +76,8 @@ struct bb_engine
   bb_pfsp_dev T;
   void *table_mem;
   int lb, n, m, prefilter;
+  int table;           /* LB2: subset-table kernel (pfsp_expand<3,MM>) */
+  void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
   /* N-Queens */
@@ -106,6 +108,7 @@ extern "C" void bb_config_default(bb_config *cfg)
   cfg->lb2_prefilter = 1;
   cfg->lb2_staged = 1;
   cfg->lb2_stage_a = 8;
+  cfg->lb2_table = 1;
 }
 
 /* ------------------------------------------------------------------ small kernels: plan / seed / export */
@@ -135,6 +138,65 @@ __global__ void k_reset(bb_ctrl *c, int best, int M, int capacity, int maxkids)
 }
 
 __global__ void k_set_best(bb_ctrl *c, int best) { atomicMin(&c->best, best); }
+
+/* Subset table of LB2 (bb_pfsp_kernels.cuh, LB = 3): one thread per unscheduled set U walks every machine pair's
+ * Johnson order once with the head-independent recurrence (D starts at -inf, so only the max_k(b_k + suffix a)
+ * term survives) and keeps, per first machine, the largest value plus the second machine's tail. */
+__global__ void __launch_bounds__(256) k_lb2_build_table(bb_pfsp_dev T, uint16_t *__restrict__ g16, int grow)
+{
+  extern __shared__ __align__(16) unsigned char sm[];
+  const int P = T.P, n = T.n, m = T.m;
+  uint32_t *jbit = reinterpret_cast<uint32_t *>(sm);
+  int *ja = reinterpret_cast<int *>(jbit + P * BB_MAX_JOBS);
+  int *jb = ja + P * BB_MAX_JOBS;
+  int2 *pairs = reinterpret_cast<int2 *>(jb + P * BB_MAX_JOBS);
+  int *tails = reinterpret_cast<int *>(pairs + P);
+  int *G = tails + BB_MAX_MACHINES; /* [BB_MAX_MACHINES][256] */
+  for (int i = threadIdx.x; i < P * BB_MAX_JOBS; i += blockDim.x)
+  {
+    jbit[i] = T.jbit[i];
+    ja[i] = T.ja[i];
+    jb[i] = T.jb[i];
+  }
+  for (int i = threadIdx.x; i < P; i += blockDim.x)
+    pairs[i] = T.pairs[i];
+  for (int i = threadIdx.x; i < m; i += blockDim.x)
+    tails[i] = T.tails[i];
+  for (int a = 0; a < BB_MAX_MACHINES; a++)
+    G[a * 256 + threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t U = blockIdx.x * blockDim.x + threadIdx.x;
+  if (U >= (1u << n))
+    return;
+  const int NEG = -(1 << 28);
+  for (int s = 0; s < P; s++)
+  {
+    int D = NEG;
+    const uint4 *vbit = reinterpret_cast<const uint4 *>(jbit + s * BB_MAX_JOBS);
+    const int4 *va = reinterpret_cast<const int4 *>(ja + s * BB_MAX_JOBS);
+    const int4 *vb = reinterpret_cast<const int4 *>(jb + s * BB_MAX_JOBS);
+#pragma unroll
+    for (int q = 0; q < BB_MAX_JOBS / 4; q++)
+    {
+      const uint4 bits = vbit[q];
+      const int4 a4 = va[q];
+      const int4 b4 = vb[q];
+      if (U & bits.x) D = bbk::add_max(D, a4.x, b4.x);
+      if (U & bits.y) D = bbk::add_max(D, a4.y, b4.y);
+      if (U & bits.z) D = bbk::add_max(D, a4.z, b4.z);
+      if (U & bits.w) D = bbk::add_max(D, a4.w, b4.w);
+    }
+    const int2 ab = pairs[s];
+    const int v = D + tails[ab.y];
+    if (v > G[ab.x * 256 + threadIdx.x])
+      G[ab.x * 256 + threadIdx.x] = v;
+  }
+  for (int a = 0; a < grow; a++)
+  {
+    const int v = a < m - 1 ? G[a * 256 + threadIdx.x] : 0;
+    g16[(size_t)U * grow + a] = (uint16_t)(v > 65535 ? 65535 : v);
+  }
+}
 
 /* LB2 staged kernel: forget the learned pair order (identity order, zero scores and histogram) */
 __global__ void k_lb2_reset_order(bb_pfsp_dev T)
@@ -465,7 +527,8 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
   e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
-  e->staged = (lb == 2) && (cfg ? (cfg->lb2_staged != 0) : 1) && ins->nb_machine_pairs > 0;
+  e->table = (lb == 2) && (cfg ? (cfg->lb2_table != 0) : 1) && ins->nb_machine_pairs > 0;
+  e->staged = (lb == 2) && !e->table && (cfg ? (cfg->lb2_staged != 0) : 1) && ins->nb_machine_pairs > 0;
   e->stage_a = cfg && cfg->lb2_stage_a > 0 ? cfg->lb2_stage_a : 8;
   int rc = alloc_common(e, cfg, bbk::pfsp_planes(e->m), 0);
   if (rc)
@@ -474,6 +537,27 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   if (rc)
     return rc;
   const int mm = bbk::pfsp_mm(e->m);
+  if (e->table)
+  {
+    /* build the subset table once per engine: 2^n rows of grow uint16 (part of the instance tables, like the
+     * Johnson schedules the reference precomputes on the host) */
+    const int grow = ((e->m - 1) + 7) & ~7;
+    const size_t rows = (size_t)1 << e->n;
+    BB_CUDA_TRY(cudaMalloc(&e->g16_mem, rows * grow * sizeof(uint16_t)));
+    e->table_bytes += rows * grow * sizeof(uint16_t);
+    const int P = e->T.P;
+    const size_t sm = (size_t)P * BB_MAX_JOBS * 12 + (size_t)P * 8 + BB_MAX_MACHINES * 4 + BB_MAX_MACHINES * 256 * 4;
+    BB_CUDA_TRY(cudaFuncSetAttribute(k_lb2_build_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    k_lb2_build_table<<<(unsigned)((rows + 255) / 256), 256, sm, e->stream>>>(e->T, (uint16_t *)e->g16_mem, grow);
+    BB_CUDA_TRY(cudaGetLastError());
+    BB_CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->T.g16 = (const uint16_t *)e->g16_mem;
+    e->T.grow = grow;
+    rc = setup_launch(e, pick_pfsp_kernel<3>(mm), bbk::pfsp_layout(e->m, e->T.P, 3).total);
+    if (rc)
+      return rc;
+    return build_graph(e);
+  }
   if (e->staged)
   {
     const void *k = mm == 5    ? (const void *)bbk::pfsp_expand_lb2<5>
@@ -577,6 +661,8 @@ extern "C" void bb_engine_destroy(bb_engine *e)
   }
   if (e->table_mem)
     cudaFree(e->table_mem);
+  if (e->g16_mem)
+    cudaFree(e->g16_mem);
   if (e->ctrl)
     cudaFree(e->ctrl);
   if (e->ctrl_h)

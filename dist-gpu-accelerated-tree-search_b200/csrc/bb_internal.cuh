@@ -89,6 +89,10 @@ struct bb_pfsp_dev
   int *order;
   unsigned *score;
   unsigned *hist;
+  /* subset-table LB2 (see k_lb2_build_table in bb_engine.cu): g16[U * grow + a] = max over pairs (a, b) of the
+   * head-independent part of the pair's Johnson makespan on the unscheduled set U, plus min_tails[b] */
+  const uint16_t *g16;
+  int grow; /* u16 per row (m - 1 rounded up to a multiple of 8) */
   int best_known;
 };
 

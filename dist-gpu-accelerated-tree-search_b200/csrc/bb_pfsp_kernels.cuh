@@ -24,6 +24,17 @@
  *                   t0's final value is front[a] + remain[a], known without the loop. A child is pruned as soon
  *                   as one pair reaches `best`; that is the same decision as the reference's
  *                   "break when lb > best, keep iff lb < best".
+ *   LB = 3  LB2 through the SUBSET TABLE (same decision as LB = 2, no pair loop). Unrolling the recurrence gives
+ *                   D_final = max( D0 + sum_{j in U} a_j ,  max_{k in U} ( b_k + sum_{j in U after k} a_j ) )
+ *                   over the unscheduled set U in the pair's Johnson order. The first term is
+ *                   (front+remain)[m2] - (front+remain)[m1]; the second, M_s(U), depends ONLY on the set U and the
+ *                   pair - not on the order of the scheduled prefix, so all nodes with the same unscheduled set
+ *                   share it. The pair's value becomes
+ *                     max( fr[m2] + tail[m2], fr[m1] + tail[m1], fr[m1] + M_s(U) + tail[m2] ),  fr = front + remain,
+ *                   whose first two terms are LB1_d terms. Hence
+ *                     LB2 = max( LB1_d , max_{m1 < m-1} ( fr[m1] + G_m1(U) ) ),  G_m1(U) = max_{m2 > m1} ( M_(m1,m2)(U) + tail[m2] ),
+ *                   and G is a table of 2^n x (m-1) uint16 built once per instance on the device (42 MB at 20x20,
+ *                   resident in the 126 MB L2). A child bound is then one 48-byte row read and m-1 add/max.
  *   The root (depth 0) is stored with front = 0; the reference's LB1_d uses min_heads there
  *   (c_bound_simple.c:57-61), which gives the same values because a job can never reach machine i before
  *   min_heads[i].
@@ -199,7 +210,7 @@ __device__ __forceinline__ bool finish_iteration(bb_ctrl *ctrl, unsigned long lo
 }
 
 template <int LB, int MM>
-__global__ void __launch_bounds__(BB_CTA_THREADS, (LB == 2 ? 2 : 3))
+__global__ void __launch_bounds__(BB_CTA_THREADS, (LB >= 2 ? 2 : 3)) /* LB 3 = LB2 through the subset table */
 pfsp_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T, const int prefilter)
 {
   const int nbatch = ctrl->n;
@@ -355,6 +366,35 @@ pfsp_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T,
           atomicMin(&ctrl->best, lb);
       }
       bool keep = act && !leaf && (lb < best);
+
+      if (LB == 3)
+      {
+        /* LB2 = max(LB1_d, max_a(fr[a] + G_a(U))): the LB1_d test above is exact as a prefilter */
+        const bool cand = prefilter ? keep : (act && !leaf);
+        if (cand)
+        {
+          const uint32_t U = ~((pw5 >> 8) | (1u << job)) & ((1u << n) - 1u);
+          const uint4 *row = reinterpret_cast<const uint4 *>(T.g16 + (size_t)U * T.grow);
+          constexpr int NV = (MU - 1 + 7) / 8; /* uint4 loads per row */
+          int v = lb;
+#pragma unroll
+          for (int q = 0; q < NV; q++)
+          {
+            const uint4 g = __ldg(row + q);
+            const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+            for (int h = 0; h < 8; h++)
+            {
+              const int a = q * 8 + h;
+              if (a < MU - 1 && (MM || a < m - 1))
+                v = max(v, fc[a] + rc[a] + (int)((gw[h >> 1] >> (16 * (h & 1))) & 0xffffu));
+            }
+          }
+          keep = v < best;
+          cnt6[4]++;
+          cnt6[5] += P;
+        }
+      }
 
       if (LB == 2)
       {

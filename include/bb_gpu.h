@@ -165,6 +165,8 @@ typedef struct bb_config
   int lb2_staged;         /* LB2 only: 1 = staged kernel with learned pair order and candidate compaction (default),
                              0 = first-generation kernel walking the pairs in the reference's order */
   int lb2_stage_a;        /* LB2 staged kernel: pairs tried before the survivors are compacted; <=0: 8 */
+  int lb2_table;          /* LB2 only: 1 = evaluate LB2 through the per-instance subset table (default; 2^n rows,
+                             42 MB at 20x20, built on the device at engine creation), 0 = walk the machine pairs */
 } bb_config;
 
 typedef struct bb_stats
