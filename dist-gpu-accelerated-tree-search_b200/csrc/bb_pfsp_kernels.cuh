@@ -77,8 +77,8 @@ __host__ __device__ inline int pfsp_planes(int m) { return (6 + pfsp_mp(m) + 3) 
 
 struct pfsp_smem_layout
 {
-  int off_p8, off_tails, off_jbit, off_ja, off_jb, off_pairs, off_warp, warp_bytes, off_tile, off_offs, off_fc,
-      off_fr, total;
+  int off_p8, off_tails, off_jbit, off_ja, off_jb, off_pairs, off_warp, warp_bytes, off_tile, off_offs, off_surv,
+      off_fc, off_fr, total;
 };
 
 __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb)
@@ -108,6 +108,8 @@ __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb)
   w += pfsp_planes(m) * BB_TILE_MAX * 16;
   L.off_offs = w;
   w += 36 * 4;
+  L.off_surv = w; /* survivors of the tile: (parent << 8) | slot, at most 32 parents x BB_MAX_JOBS children */
+  w += BB_TILE_MAX * BB_MAX_JOBS * 2;
   L.off_fc = L.off_fr = w;
   if (lb == 2)
   {
@@ -237,6 +239,7 @@ pfsp_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T,
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
   uint4 *tile_s = reinterpret_cast<uint4 *>(wbase + L.off_tile);   /* [plane][32] */
   int *offs_s = reinterpret_cast<int *>(wbase + L.off_offs);       /* [33] exclusive child offsets */
+  uint16_t *surv_s = reinterpret_cast<uint16_t *>(wbase + L.off_surv); /* survivors of the tile */
   uint16_t *fc_s = reinterpret_cast<uint16_t *>(wbase + L.off_fc); /* [MP][32] child front        (LB2) */
   uint16_t *fr_s = reinterpret_cast<uint16_t *>(wbase + L.off_fr); /* [MP][32] child front+remain (LB2) */
 
@@ -297,6 +300,8 @@ pfsp_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T,
     }
     __syncwarp();
 
+    /* ---- pass 1: bound every child of the tile, remember the survivors ---- */
+    int nsurv = 0;
     for (int c0 = 0; c0 < total; c0 += 32)
     {
       const int c = c0 + lane;
@@ -455,62 +460,98 @@ pfsp_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T,
         }
       }
 
-      /* ---- prune + branch + compact: warp-aggregated append of the survivors ---- */
+      /* ---- prune: survivors are only recorded here; they are branched and written in pass 2 ---- */
       const unsigned kmask = __ballot_sync(0xffffffffu, keep);
-      if (kmask)
+      if (keep)
+        surv_s[nsurv + __popc(kmask & ((1u << lane) - 1u))] = (uint16_t)((p << 8) | k);
+      nsurv += __popc(kmask);
+    }
+    __syncwarp();
+
+    /* ---- pass 2: ONE reservation on the destination cursor per tile (not per 32 children: the cursor is a single
+     * address every warp of the grid hits), then branch + compact with every lane writing a survivor: the child's
+     * front/remain are recomputed from the parent (survivors are ~1 child in 10), the planes go out as full
+     * 512-byte coalesced stores ---- */
+    if (nsurv)
+    {
+      unsigned pos = 0;
+      if (lane == 0)
       {
-        const int nk = __popc(kmask);
-        unsigned pos = 0;
-        if (lane == 0)
-          pos = atomicAdd(&ctrl->tail, (unsigned)nk);
-        pos = __shfl_sync(0xffffffffu, pos, 0);
-        if (pos + (unsigned)nk > (unsigned)cap)
-        {
-          if (lane == 0)
-            atomicExch(&ctrl->error, 1);
-        }
-        else if (keep)
-        {
-          cnt6[0]++;
-          const size_t slot = (size_t)pos + __popc(kmask & ((1u << lane) - 1u));
-          /* child record: prmu with [depth] <-> [k] swapped (xor patch), depth+1 | scheduled mask, front, remain */
-          uint32_t w[NPL * 4];
-          const uint4 q0 = tile_s[p];
-          w[0] = q0.x;
-          w[1] = q0.y;
-          w[2] = q0.z;
-          w[3] = q0.w;
-          w[4] = *reinterpret_cast<const uint32_t *>(rec + 512);
-          const uint32_t x = (uint32_t)(job ^ jobd);
-#pragma unroll
-          for (int wi = 0; wi < 5; wi++)
-          {
-            uint32_t patch = 0;
-            if (wi == (depth >> 2))
-              patch ^= x << (8 * (depth & 3));
-            if (wi == (k >> 2))
-              patch ^= x << (8 * (k & 3));
-            w[wi] ^= patch;
-          }
-          w[5] = (uint32_t)(depth + 1) | (((pw5 >> 8) | (1u << job)) << 8);
-#pragma unroll
-          for (int i = 0; i < MP; i += 2)
-          {
-            const uint32_t f_lo = i < MU ? (uint32_t)fc[i < MU ? i : 0] : 0u;
-            const uint32_t f_hi = i + 1 < MU ? (uint32_t)fc[i + 1 < MU ? i + 1 : 0] : 0u;
-            const uint32_t r_lo = i < MU ? (uint32_t)rc[i < MU ? i : 0] : 0u;
-            const uint32_t r_hi = i + 1 < MU ? (uint32_t)rc[i + 1 < MU ? i + 1 : 0] : 0u;
-            w[6 + i / 2] = f_lo | (f_hi << 16);
-            w[6 + MP / 2 + i / 2] = r_lo | (r_hi << 16);
-          }
-#pragma unroll
-          for (int wi = 6 + MP; wi < NPL * 4; wi++)
-            w[wi] = 0u;
-#pragma unroll
-          for (int q = 0; q < NPL; q++)
-            dplanes[(size_t)q * cap + slot] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-        }
+        pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
+        cnt6[0] += nsurv;
       }
+      pos = __shfl_sync(0xffffffffu, pos, 0);
+      if (pos + (unsigned)nsurv > (unsigned)cap)
+      {
+        if (lane == 0)
+          atomicExch(&ctrl->error, 1);
+      }
+      else
+        for (int i0 = 0; i0 < nsurv; i0 += 32)
+        {
+          const int i = i0 + lane;
+          if (i < nsurv)
+          {
+            const int e = surv_s[i];
+            const int p = e >> 8, k = e & 0xff;
+            const unsigned char *rec = reinterpret_cast<const unsigned char *>(tile_s) + p * 16;
+            const uint32_t pw5 = *reinterpret_cast<const uint32_t *>(rec + 512 + 4);
+            const int depth = pw5 & 0xffu;
+            const int job = rec[(k >> 4) * 512 + (k & 15)];
+            const int jobd = rec[(depth >> 4) * 512 + (depth & 15)];
+            auto rd16 = [&](int idx) -> int {
+              return *reinterpret_cast<const uint16_t *>(rec + ((idx * 2) >> 4) * 512 + ((idx * 2) & 15));
+            };
+            uint32_t w[NPL * 4];
+            const uint4 q0 = tile_s[p];
+            w[0] = q0.x;
+            w[1] = q0.y;
+            w[2] = q0.z;
+            w[3] = q0.w;
+            w[4] = *reinterpret_cast<const uint32_t *>(rec + 512);
+            const uint32_t x = (uint32_t)(job ^ jobd);
+#pragma unroll
+            for (int wi = 0; wi < 5; wi++)
+            {
+              uint32_t patch = 0;
+              if (wi == (depth >> 2))
+                patch ^= x << (8 * (depth & 3));
+              if (wi == (k >> 2))
+                patch ^= x << (8 * (k & 3));
+              w[wi] ^= patch;
+            }
+            w[5] = (uint32_t)(depth + 1) | (((pw5 >> 8) | (1u << job)) << 8);
+            /* child front / remain (the same recurrence as in pass 1) */
+            int t = 0;
+#pragma unroll
+            for (int i2 = 0; i2 < MP; i2 += 2)
+            {
+              uint32_t f2 = 0, r2 = 0;
+#pragma unroll
+              for (int h = 0; h < 2; h++)
+              {
+                const int mi = i2 + h;
+                if (mi < MU && (MM || mi < m))
+                {
+                  const int fi = rd16(12 + mi), ri = rd16(12 + MP + mi);
+                  const int pji = p8[mi * BB_MAX_JOBS + job];
+                  t = (mi == 0 ? fi : max(t, fi)) + pji;
+                  f2 |= (uint32_t)t << (16 * h);
+                  r2 |= (uint32_t)(ri - pji) << (16 * h);
+                }
+              }
+              w[6 + i2 / 2] = f2;
+              w[6 + MP / 2 + i2 / 2] = r2;
+            }
+#pragma unroll
+            for (int wi = 6 + MP; wi < NPL * 4; wi++)
+              w[wi] = 0u;
+            const size_t slot = (size_t)pos + i;
+#pragma unroll
+            for (int q = 0; q < NPL; q++)
+              dplanes[(size_t)q * cap + slot] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+          }
+        }
     }
     __syncwarp();
   }
