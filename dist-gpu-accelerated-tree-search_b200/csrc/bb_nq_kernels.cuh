@@ -5,9 +5,15 @@
  * generate_children + pushBack (nqueens/nqueens_multigpu_cuda.cu:288-314, kernel :158-186, branch :189-210).
  *
  * Same warp-tile mapping as the PFSP kernel: a warp loads <= 32 parents (coalesced), prefix-sums N - depth, then
- * evaluates the candidate slots 32 at a time with one lane per (parent, slot). isSafe is the reference's diagonal
- * test on int-promoted values (nqueens_c.c:80-96), really executed G times per placed queen (-g is the
- * reference's arithmetic-intensity knob, README "safety checks per evaluation").
+ * evaluates the candidate slots 32 at a time with one lane per (parent, slot).
+ *
+ * isSafe (nqueens_c.c:80-96) asks whether a queen at (column depth, row r) shares a diagonal with one of the placed
+ * queens (column i, row b_i): b_i == r - (depth - i) or b_i == r + (depth - i), i.e. b_i + i == r + depth or
+ * b_i - i == r - depth. The lane that loaded a parent folds its placed queens ONCE into two occupancy words
+ * (diagonal b+i and anti-diagonal b-i+N-1, < 2N-1 <= 39 bits each); a candidate is then two bit tests instead of
+ * a loop over the placed queens that every one of the N-depth candidates of the parent would repeat. The labels
+ * are identical to the reference's. -g (the reference's "safety checks per evaluation" knob) repeats the test G
+ * times behind an opaque register barrier, so the work still scales with G.
  *
  * Children at depth N are solutions: the reference pushes them, counts them in exploredTree, and counts
  * exploredSol when they are popped (nqueens_c.c:103-105, 112-113). Here they are counted in both at generation and
@@ -42,8 +48,12 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
   /* per warp: 32 rows of 32 bytes (board bytes 0..23 used), offsets [33] */
   __shared__ __align__(16) unsigned char rows_s[BB_WARPS_PER_CTA][32 * 32];
   __shared__ int offs_all[BB_WARPS_PER_CTA][36];
+  __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS]; /* (parent << 8) | slot */
+  __shared__ unsigned long long diag_all[BB_WARPS_PER_CTA][2][32]; /* per parent: occupied diagonals / anti-diagonals */
   unsigned char *rows = rows_s[warp];
   int *offs_s = offs_all[warp];
+  uint16_t *surv_s = surv_all[warp];
+  unsigned long long *d1_s = diag_all[warp][0], *d2_s = diag_all[warp][1];
 
   const uint4 *__restrict__ splane = pool.planes[src];
   uint4 *__restrict__ dplane = pool.planes[dst];
@@ -65,7 +75,17 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
 #pragma unroll
       for (int t = 0; t < TW; t++)
         *reinterpret_cast<uint32_t *>(rows + lane * 32 + 16 + 4 * t) = stail[node * TW + t];
-      kids = N - (int)rows[lane * 32 + dbyte];
+      const int depth = rows[lane * 32 + dbyte];
+      kids = N - depth;
+      unsigned long long d1 = 0ull, d2 = 0ull;
+      for (int i = 0; i < depth; i++)
+      {
+        const int b = rows[lane * 32 + i];
+        d1 |= 1ull << (b + i);
+        d2 |= 1ull << (b - i + N - 1);
+      }
+      d1_s[lane] = d1;
+      d2_s[lane] = d2;
     }
     const int incl = warp_incl_scan(kids, lane);
     const int total = __shfl_sync(0xffffffffu, incl, 31);
@@ -78,6 +98,8 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
     }
     __syncwarp();
 
+    /* ---- pass 1: evaluate every candidate slot of the tile, remember the safe inner placements ---- */
+    int nsurv = 0;
     for (int c0 = 0; c0 < total; c0 += 32)
     {
       const int c = c0 + lane;
@@ -95,17 +117,14 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
       const int k = act ? depth + (c - offs_s[p]) : depth;
       const int cand = row[k]; /* row position tried for column `depth` */
 
-      /* isSafe: nqueens_c.c:80-96 / nqueens_multigpu_cuda.cu:170-183 */
+      /* isSafe: nqueens_c.c:80-96 / nqueens_multigpu_cuda.cu:170-183, as two diagonal-occupancy tests */
+      const unsigned long long d1 = d1_s[p], d2 = d2_s[p];
       int safe = 1;
-      for (int i = 0; i < depth; i++)
+      int r = cand;
+      for (int g = 0; g < G; g++)
       {
-        int other = row[i];
-        const int d = depth - i;
-        for (int g = 0; g < G; g++)
-        {
-          asm volatile("" : "+r"(other)); /* keep the G repetitions as real work, as the reference's -g intends */
-          safe &= (other != cand - d) & (other != cand + d);
-        }
+        asm volatile("" : "+r"(r)); /* keep the G repetitions as real work, as the reference's -g intends */
+        safe &= (int)(((d1 >> (r + depth)) | (d2 >> (r - depth + N - 1))) & 1ull) ^ 1;
       }
       const bool ok = act && safe;
       const bool leaf = (depth + 1 == N);
@@ -117,51 +136,66 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
       }
       const bool keep = ok && !leaf;
       const unsigned kmask = __ballot_sync(0xffffffffu, keep);
-      if (kmask)
+      if (keep)
+        surv_s[nsurv + __popc(kmask & ((1u << lane) - 1u))] = (uint16_t)((p << 8) | k);
+      nsurv += __popc(kmask);
+    }
+    __syncwarp();
+
+    /* ---- pass 2: one reservation on the destination cursor per tile, then every lane writes one child ---- */
+    if (nsurv)
+    {
+      unsigned pos = 0;
+      if (lane == 0)
+        pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
+      pos = __shfl_sync(0xffffffffu, pos, 0);
+      if (pos + (unsigned)nsurv > (unsigned)cap)
       {
-        const int nk = __popc(kmask);
-        unsigned pos = 0;
         if (lane == 0)
-          pos = atomicAdd(&ctrl->tail, (unsigned)nk);
-        pos = __shfl_sync(0xffffffffu, pos, 0);
-        if (pos + (unsigned)nk > (unsigned)cap)
-        {
-          if (lane == 0)
-            atomicExch(&ctrl->error, 1);
-        }
-        else if (keep)
-        {
-          const size_t slot = (size_t)pos + __popc(kmask & ((1u << lane) - 1u));
-          uint32_t w[4 + (TW ? TW : 1)];
-          const uint4 q0 = *reinterpret_cast<const uint4 *>(row);
-          w[0] = q0.x;
-          w[1] = q0.y;
-          w[2] = q0.z;
-          w[3] = q0.w;
-#pragma unroll
-          for (int t = 0; t < TW; t++)
-            w[4 + t] = *reinterpret_cast<const uint32_t *>(row + 16 + 4 * t);
-          /* swap board[depth] <-> board[k] (xor patch), then depth+1 (depth byte xor old^new) */
-          const uint32_t x = (uint32_t)(cand ^ row[depth]);
-          const uint32_t dx = (uint32_t)(depth ^ (depth + 1));
-#pragma unroll
-          for (int wi = 0; wi < 4 + TW; wi++)
-          {
-            uint32_t patch = 0;
-            if (wi == (depth >> 2))
-              patch ^= x << (8 * (depth & 3));
-            if (wi == (k >> 2))
-              patch ^= x << (8 * (k & 3));
-            if (wi == (dbyte >> 2))
-              patch ^= dx << (8 * (dbyte & 3));
-            w[wi] ^= patch;
-          }
-          dplane[slot] = make_uint4(w[0], w[1], w[2], w[3]);
-#pragma unroll
-          for (int t = 0; t < TW; t++)
-            dtail[slot * TW + t] = w[4 + t];
-        }
+          atomicExch(&ctrl->error, 1);
       }
+      else
+        for (int i0 = 0; i0 < nsurv; i0 += 32)
+        {
+          const int i = i0 + lane;
+          if (i < nsurv)
+          {
+            const int e = surv_s[i];
+            const int p = e >> 8, k = e & 0xff;
+            const unsigned char *row = rows + p * 32;
+            const int depth = row[dbyte];
+            const int cand = row[k];
+            const size_t slot = (size_t)pos + i;
+            uint32_t w[4 + (TW ? TW : 1)];
+            const uint4 q0 = *reinterpret_cast<const uint4 *>(row);
+            w[0] = q0.x;
+            w[1] = q0.y;
+            w[2] = q0.z;
+            w[3] = q0.w;
+#pragma unroll
+            for (int t = 0; t < TW; t++)
+              w[4 + t] = *reinterpret_cast<const uint32_t *>(row + 16 + 4 * t);
+            /* swap board[depth] <-> board[k] (xor patch), then depth+1 (depth byte xor old^new) */
+            const uint32_t x = (uint32_t)(cand ^ row[depth]);
+            const uint32_t dx = (uint32_t)(depth ^ (depth + 1));
+#pragma unroll
+            for (int wi = 0; wi < 4 + TW; wi++)
+            {
+              uint32_t patch = 0;
+              if (wi == (depth >> 2))
+                patch ^= x << (8 * (depth & 3));
+              if (wi == (k >> 2))
+                patch ^= x << (8 * (k & 3));
+              if (wi == (dbyte >> 2))
+                patch ^= dx << (8 * (dbyte & 3));
+              w[wi] ^= patch;
+            }
+            dplane[slot] = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+            for (int t = 0; t < TW; t++)
+              dtail[slot * TW + t] = w[4 + t];
+          }
+        }
     }
     __syncwarp();
   }
