@@ -60,7 +60,8 @@ class Stats(C.Structure):
                 ("iterations", C.c_ulonglong), ("launches", C.c_ulonglong), ("pool_size", C.c_longlong),
                 ("max_pool", C.c_longlong), ("best", C.c_int), ("kernel_ms", C.c_double), ("span_ms", C.c_double),
                 ("h2d_bytes", C.c_ulonglong), ("d2h_bytes", C.c_ulonglong), ("table_bytes", C.c_ulonglong),
-                ("grid", C.c_int), ("smem_bytes", C.c_int), ("record_bytes", C.c_int)]
+                ("grid", C.c_int), ("smem_bytes", C.c_int), ("record_bytes", C.c_int),
+                ("steals", C.c_ulonglong), ("steals_ok", C.c_ulonglong), ("donated", C.c_ulonglong)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -69,7 +70,8 @@ class Stats(C.Structure):
 class SearchResult(C.Structure):
     _fields_ = [("tree", C.c_ulonglong), ("sol", C.c_ulonglong), ("best", C.c_int), ("elapsed_s", C.c_double),
                 ("kernel_ms_max", C.c_double), ("steals", C.c_ulonglong), ("steals_ok", C.c_ulonglong),
-                ("search_s", C.c_double), ("nodes_moved", C.c_ulonglong)]
+                ("search_s", C.c_double), ("nodes_moved", C.c_ulonglong), ("warm_tree", C.c_ulonglong),
+                ("warm_sol", C.c_ulonglong), ("warm_s", C.c_double), ("setup_s", C.c_double)]
 
 
 class TeamResult(C.Structure):

@@ -853,6 +853,7 @@ static void fill_stats(bb_engine *e, bb_stats *out)
   out->grid = e->grid;
   out->smem_bytes = e->smem;
   out->record_bytes = e->pool.nplanes * 16 + e->pool.tail_words * 4;
+  out->steals = out->steals_ok = out->donated = 0;
 }
 
 extern "C" int bb_engine_get_stats(bb_engine *e, bb_stats *out)

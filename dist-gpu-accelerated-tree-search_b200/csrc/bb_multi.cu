@@ -231,6 +231,7 @@ int search_single(int kind, const bb_pfsp_instance *ins, int lb, int best0, int 
   res->best = st.best;
   res->elapsed_s = now_s() - t0;
   res->search_s = t2 - t1;
+  res->setup_s = t1 - t0;
   res->kernel_ms_max = st.kernel_ms;
   if (per_gpu)
     per_gpu[0] = st;
@@ -239,6 +240,7 @@ int search_single(int kind, const bb_pfsp_instance *ins, int lb, int best0, int 
 
 struct thread_out
 {
+  double setup_s, warm_s;
   int rc;
   char err[256];
   bb_stats st;
@@ -301,7 +303,9 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         strncpy(o.err, bb_last_error(), sizeof(o.err) - 1);
         bb_team_fail(team);
       };
+      const double c0 = now_s();
       w.e = create_engine(kind, ins, lb, N, G, &c, i);
+      o.setup_s = now_s() - c0;
       if (!w.e)
         fail(BB_ERR_CUDA);
       if (bb_team_barrier(team, 120) != BB_OK || o.rc)
@@ -318,7 +322,9 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         bb_engine_pool_info(W[j].e, w.peers[j].planes, w.peers[j].tailw, &w.peers[j].capacity, &dev);
       }
       int best = best0;
+      const double w0 = now_s();
       int rc = seed_partition(w.e, kind, D, i, m_keep, best0, &o.base_tree, &o.base_sol, &best);
+      o.warm_s = now_s() - w0;
       if (rc)
         fail(rc);
       if (bb_team_barrier(team, 120) == BB_OK && !o.rc)
@@ -334,7 +340,12 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         if (rc)
           fail(rc);
         else
+        {
           bb_engine_get_stats(w.e, &o.st);
+          o.st.steals = o.tr.steals;
+          o.st.steals_ok = o.tr.steals_ok;
+          o.st.donated = o.tr.donated;
+        }
       }
       bb_team_barrier(team, 120); /* nobody frees a pool a peer may still be reading */
       bb_engine_destroy(w.e);
@@ -364,6 +375,15 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
   }
   res->tree += out[0].base_tree;
   res->sol += out[0].base_sol;
+  res->warm_tree = out[0].base_tree;
+  res->warm_sol = out[0].base_sol;
+  for (int i = 0; i < D; i++)
+  {
+    if (out[i].warm_s > res->warm_s)
+      res->warm_s = out[i].warm_s;
+    if (out[i].setup_s > res->setup_s)
+      res->setup_s = out[i].setup_s;
+  }
   res->elapsed_s = now_s() - t0;
   free(team);
   return rc;
@@ -381,8 +401,8 @@ struct ipc_slot
   int has_tail;
   long long capacity;
   /* results */
-  unsigned long long tree, sol, steals, steals_ok, donated;
-  double kernel_ms, search_s;
+  unsigned long long tree, sol, steals, steals_ok, donated, warm_tree, warm_sol;
+  double kernel_ms, search_s, warm_s, setup_s;
   int best, rc;
 };
 
@@ -430,9 +450,12 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     rc = code;
     bb_team_fail(mem);
   };
+  double setup_s = 0, warm_s = 0;
   if (!rc)
   {
+    const double c0 = now_s();
     w.e = create_engine(kind, ins, lb, N, G, &c, c.device);
+    setup_s = now_s() - c0;
     if (!w.e)
       fail(BB_ERR_CUDA);
   }
@@ -484,7 +507,9 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   int best = best0;
   if (!rc)
   {
+    const double w0 = now_s();
     const int r2 = seed_partition(w.e, kind, world, rank, m_keep, best0, &base_tree, &base_sol, &best);
+    warm_s = now_s() - w0;
     if (r2)
       fail(r2);
   }
@@ -512,7 +537,14 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   I[rank].donated = tr.donated;
   I[rank].kernel_ms = st.kernel_ms;
   I[rank].search_s = search_s;
+  I[rank].warm_s = warm_s;
+  I[rank].setup_s = setup_s;
+  I[rank].warm_tree = rank == 0 ? base_tree : 0;
+  I[rank].warm_sol = rank == 0 ? base_sol : 0;
   I[rank].best = tr.best;
+  st.steals = tr.steals;
+  st.steals_ok = tr.steals_ok;
+  st.donated = tr.donated;
   I[rank].rc = rc;
   const int b1 = bb_team_barrier(mem, 180);
   memset(res, 0, sizeof(*res));
@@ -529,6 +561,12 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
         res->kernel_ms_max = I[j].kernel_ms;
       if (I[j].search_s > res->search_s)
         res->search_s = I[j].search_s;
+      if (I[j].warm_s > res->warm_s)
+        res->warm_s = I[j].warm_s;
+      if (I[j].setup_s > res->setup_s)
+        res->setup_s = I[j].setup_s;
+      res->warm_tree += I[j].warm_tree;
+      res->warm_sol += I[j].warm_sol;
       if (I[j].best < res->best)
         res->best = I[j].best;
       if (I[j].rc && !rc)

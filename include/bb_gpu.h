@@ -190,6 +190,8 @@ typedef struct bb_stats
   int grid;                       /* CTAs per launch (a multiple of the SM count) */
   int smem_bytes;                 /* dynamic shared memory per CTA */
   int record_bytes;               /* bytes one node occupies in the device pool */
+  unsigned long long steals, steals_ok, donated; /* whole searches on D > 1 GPUs: this worker's steal attempts,
+                                                    successes, and nodes it gave away */
 } bb_stats;
 
 void bb_config_default(bb_config *cfg);
@@ -225,6 +227,10 @@ typedef struct bb_search_result
   double search_s;      /* max over GPUs of the wall time from the common start barrier (pools seeded, tables
                            resident) to the detection of global termination */
   unsigned long long nodes_moved; /* nodes that changed GPU through work stealing */
+  /* phase split, as the reference drivers print it (pfsp_multigpu_cuda.c:120-125, 476-481, 503-508) */
+  unsigned long long warm_tree, warm_sol; /* counted during the common warm-up (step 1; on the GPU here) */
+  double warm_s;                          /* engine creation excluded: warm-up expansion + partition */
+  double setup_s;                         /* engine creation: pool cudaMalloc, table upload, LB2 table build */
 } bb_search_result;
 
 int bb_pfsp_search(const bb_pfsp_instance *ins, int lb, int best0, int D, int ws, const bb_config *cfg,

@@ -102,6 +102,61 @@ def test_lb2_prefilter_does_not_change_counts():
     assert pb[0].lb2_evals == pb[0].evals == 1298094 > pa[0].lb2_evals  # SURVEY appendix A.2 census
 
 
+LB2_VARIANTS = {"table": dict(lb2_table=1), "staged": dict(lb2_table=0, lb2_staged=1, lb2_stage_a=4),
+                "ordered": dict(lb2_table=0, lb2_staged=0)}
+
+
+@pytest.mark.parametrize("variant", sorted(LB2_VARIANTS))
+@pytest.mark.parametrize("inst", [14, 21])
+def test_lb2_kernels_one_iteration_children_match_oracle(variant, inst):
+    """the three LB2 evaluations - subset table (default), staged pair loop with learned order, pair loop in the
+    reference's order - keep exactly the children generate_children keeps on the reference's bounds"""
+    L = orc.oracle()
+    ins = bb.Instance(inst=inst)
+    n = ins.n
+    h = L.orc_pfsp_new(inst)
+    rng = np.random.default_rng(17 * inst)
+    eng = bb.Engine.pfsp(ins, 2, M=100000, **LB2_VARIANTS[variant])
+    for best in (ins.best_known, ins.best_known + 90):
+        parents = orc.random_pfsp_nodes(rng, n, 6000, 0, n - 2)
+        eng.reset(best)
+        eng.push_nodes(parents)
+        st = eng.run(1)
+        kids, tree, sol, b, nb = oracle_one_level(h, n, 2, parents, best)
+        assert (st.tree, st.sol, st.best, st.parents, st.evals) == (tree, sol, b, len(parents), nb)
+        assert node_set(eng.export_nodes(), 2 + n) == node_set(kids, 2 + n)
+    eng.close()
+    L.orc_pfsp_free(h)
+
+
+def test_lb2_kernels_agree_on_whole_searches():
+    for inst, exp in ((14, (144639, 0, 1377)), (3, (80062, 0, 1081)), (29, (9499307, 0, 2237))):
+        ins = bb.Instance(inst=inst)
+        for name, kw in LB2_VARIANTS.items():
+            res, _ = bb.pfsp_search(ins, 2, M=1 << 18, **kw)
+            assert (res.tree, res.sol, res.best) == exp, (inst, name)
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("D", [2, 4, 8])
+def test_multi_gpu_threads_same_counts(D):
+    """D GPUs in one process (one host thread per GPU, peer-memory stealing): the counts are those of one GPU"""
+    if _gpu_count() < D:
+        pytest.skip(f"needs {D} GPUs")
+    for ws in (1, 0):
+        res, per = bb.pfsp_search(bb.Instance(inst=30), 0, D=D, ws=ws, M=1 << 18)
+        assert (res.tree, res.sol, res.best) == (111887480, 82, 2178)
+        assert sum(p.tree for p in per) + res.warm_tree == res.tree
+        res, per = bb.pfsp_search(bb.Instance(inst=29), 2, D=D, ws=ws, M=1 << 18)
+        assert (res.tree, res.sol, res.best) == (9499307, 0, 2237)
+    res, per = bb.nq_search(15, 1, D=D, M=1 << 18)
+    assert (res.tree, res.sol) == (171129071, 2279184)
+
+
 def test_custom_instance_generic_kernel_and_unknown_optimum():
     """a 9x7 matrix exercises the runtime-m kernel; start from ub = inf to find the optimum, then both
     implementations must walk the same tree from ub = optimum"""
