@@ -183,7 +183,7 @@ def kernel_key(w):
     return {0: "pfsp_expand_lb1d", 1: "pfsp_expand_lb1", 2: "pfsp_expand_lb2"}[w[2]]
 
 
-def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters, lb2_pairs, device):
+def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters, lb2_pairs, device, pairloop=False):
     """HBM roofline of the expand kernel (algorithmic bytes: every explored node is written once as a survivor and
     read once as a parent); for LB2 additionally the integer-pipe roofline in LB2 slot steps."""
     peak, peak_src = measured_peaks()
@@ -198,13 +198,16 @@ def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters,
             "algorithmic_bytes_per_node": 2 * rec_alg, "record_bytes_in_pool": rec_pool,
             "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1)}
     extra = {}
-    if w[0] == "pfsp" and w[2] == 2:
+    if w[0] == "pfsp" and w[2] == 2 and not pairloop:
+        roof["note"] = ("LB2 is evaluated through the per-instance subset table (2^n x (m-1) uint16, L2-resident): one "
+                        "48-byte row read per candidate child on top of the node records")
+    if w[0] == "pfsp" and w[2] == 2 and pairloop:
         pk = C.c_double(0)
         bb.check(bb.lib.bb_measure_slot_step_peak(device, C.byref(pk)), "bb_measure_slot_step_peak")
         steps = lb2_pairs * 20  # each evaluated (child, pair) walks the 20 Johnson slots: one bit test + one add-max
         ach = steps / (kernel_ms / 1e3)
-        roof["note"] = ("LB2 is bound by the integer ALU pipe, not HBM (ncu: ALU pipe ~69 % busy, DRAM < 2 %); the "
-                        "binding roofline is roofline_int below")
+        roof["note"] = ("the LB2 pair loop is bound by the integer ALU pipe, not HBM (ncu: ALU pipe ~69 % busy, DRAM "
+                        "< 2 %); the binding roofline is roofline_int below")
         extra["roofline_int"] = {"bound": "int_alu", "achieved": ach / 1e9, "peak": pk.value / 1e9,
                                  "unit": "G slot-steps/s", "frac": ach / pk.value,
                                  "peak_source": "measured in this run (bb_measure_slot_step_peak: LOP3 test + "
@@ -213,11 +216,16 @@ def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters,
     return roof, extra
 
 
+def lb2kw(args):
+    """--lb2-pairloop: evaluate LB2 with the staged machine-pair loop instead of the subset table (default)"""
+    return dict(lb2_table=0) if args.lb2_pairloop else {}
+
+
 def run_single(args, w, bb, torch, local_rank):
     K, W = args.steps, max(args.warmup, 0)
     if w[0] == "pfsp":
         ins = bb.Instance(inst=w[1])
-        eng = bb.Engine.pfsp(ins, w[2], device=local_rank, M=args.M)
+        eng = bb.Engine.pfsp(ins, w[2], device=local_rank, M=args.M, **lb2kw(args))
         best0 = ins.best_known
         rec_alg = ins.n + 2 + 4 * ins.m  # prmu + depth (+pad) + cached front/remain uint16[m] each
     else:
@@ -263,7 +271,7 @@ def run_single(args, w, bb, torch, local_rank):
     for _ in range(max(1, min(K, 2))):
         t = time.perf_counter()
         if w[0] == "pfsp":
-            res, per = bb.pfsp_search(ins, w[2], device=local_rank, M=args.M)
+            res, per = bb.pfsp_search(ins, w[2], device=local_rank, M=args.M, **lb2kw(args))
         else:
             res, per = bb.nq_search(w[1], 1, device=local_rank, M=args.M)
         e2e_t += time.perf_counter() - t
@@ -272,7 +280,7 @@ def run_single(args, w, bb, torch, local_rank):
         e2e_d2h = per[0].d2h_bytes
 
     roof, extra = roofline_objects(bb, w, rec_alg, st.record_bytes, parents, nodes, kernel_ms, iters, lb2_pairs,
-                                   local_rank)
+                                   local_rank, args.lb2_pairloop)
     line = {
         "metric": "explored_nodes_per_sec", "value": value, "unit": "nodes/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": span_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -290,7 +298,7 @@ def run_single(args, w, bb, torch, local_rank):
         "roofline": roof,
     }
     line.update(extra)
-    if w[0] == "pfsp" and w[2] == 2:
+    if w[0] == "pfsp" and w[2] == 2 and args.lb2_pairloop:
         line["lb2"] = {"child_bounds": evals // K, "pair_loops": lb2_evals // K, "pairs_evaluated": lb2_pairs // K,
                        "pairs_per_loop": lb2_pairs / max(lb2_evals, 1),
                        "pair_evals_per_s": lb2_pairs / (kernel_ms / 1e3)}
@@ -313,7 +321,7 @@ def run_multi(args, w, bb, torch, rank, world, local_rank):
     def one_step(i):
         name = f"{tag[0]}_{i}"
         if w[0] == "pfsp":
-            return bb.pfsp_search_dist(ins, w[2], rank, world, name, device=local_rank, M=args.M)
+            return bb.pfsp_search_dist(ins, w[2], rank, world, name, device=local_rank, M=args.M, **lb2kw(args))
         return bb.nq_search_dist(w[1], 1, rank, world, name, device=local_rank, M=args.M)
 
     for i in range(W):
@@ -357,7 +365,7 @@ def run_multi(args, w, bb, torch, rank, world, local_rank):
     if rank == 0:
         # per-kernel roofline: all ranks' algorithmic bytes over all ranks' kernel time = the average GPU's rate
         roof, extra = roofline_objects(bb, w, rec_alg, mine.record_bytes, acc["parents"], acc["nodes"],
-                                       acc["kernel_ms"], acc["iters"], acc["lb2_pairs"], local_rank)
+                                       acc["kernel_ms"], acc["iters"], acc["lb2_pairs"], local_rank, args.lb2_pairloop)
         roof["note_multi"] = "per-GPU average: bytes of all ranks / expand-kernel time summed over ranks"
         line = {
             "metric": "explored_nodes_per_sec", "value": acc["nodes"] / search_s, "unit": "nodes/s", "n_gpus": world,
@@ -401,6 +409,8 @@ def main():
     ap.add_argument("--M", type=int, default=1 << 20, help="max parents per device iteration (-M)")
     ap.add_argument("--ref-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lb2-pairloop", action="store_true",
+                    help="LB2 through the staged machine-pair loop (integer-ALU bound) instead of the subset table")
     args = ap.parse_args()
     w = parse_workload(args.workload)
     rank = int(os.environ.get("RANK", "0"))

@@ -343,13 +343,17 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   long long capacity = c.capacity;
   if (capacity <= 0)
   {
-    /* depth-first batches of M leave up to M*(branching-1) nodes behind per level: size for that, within a
-     * third of the free HBM (a B200 has 180 GB; the pool is the only large allocation of the engine) */
+    /* depth-first batches of M leave up to M*(branching-1) nodes behind per level; measured high-water marks are
+     * 20-75 x M nodes over both stacks. Size each stack to 4 GiB of records (but at least 16 x M nodes), within a
+     * third of the free HBM: pool size drives cudaMalloc / cudaFree / IPC-mapping time, which is most of the
+     * set-up cost of a short search, and the planner shrinks batches instead of overflowing near capacity. */
     size_t free_b = 0, total_b = 0;
     BB_CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
     const long long rec = (long long)nplanes * 16 + (long long)tail_words * 4;
     const long long by_mem = (long long)(free_b / 3) / (2 * rec);
-    capacity = (long long)e->M * 256;
+    capacity = (4ll << 30) / rec;
+    if (capacity < (long long)e->M * 16)
+      capacity = (long long)e->M * 16;
     if (capacity < (1 << 22))
       capacity = 1 << 22;
     if (capacity > by_mem)

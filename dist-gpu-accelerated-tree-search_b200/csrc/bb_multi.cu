@@ -19,6 +19,7 @@
 
 #include <chrono>
 #include <climits>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <thread>
@@ -161,7 +162,9 @@ int seed_partition(bb_engine *e, int kind, int D, int me, int m_keep, int best0,
     rc = bb_engine_run(e, 1, &st);
     if (rc)
       return rc;
-    if (st.pool_size == 0 || st.pool_size >= (long long)D * m_keep)
+    /* the reference stops at D*m nodes (pfsp_multigpu_cuda.c:111); a finer split costs nothing here (the
+     * warm-up runs on the GPU) and evens out the sub-tree sizes the workers start from */
+    if (st.pool_size == 0 || st.pool_size >= (long long)D * (m_keep > 2048 ? m_keep : 2048))
       break;
   }
   *base_tree = st.tree;
@@ -435,6 +438,9 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     return bb_fail(BB_ERR_STATE, "mmap(%s) failed", shm_name);
   ipc_slot *I = reinterpret_cast<ipc_slot *>(static_cast<char *>(mem) + team_sz);
   int rc = rank == 0 ? bb_team_init(mem, world) : bb_team_wait_ready(mem, world, 120);
+  const bool trace = getenv("BB_TRACE_PHASES") != nullptr; /* per-rank phase times on stderr */
+  double tp[8];
+  tp[0] = now_s();
   gpu_worker w;
   memset(&w, 0, sizeof(w));
   w.me = rank;
@@ -479,8 +485,10 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     w.peers[rank].tailw[1] = tw[1];
     w.peers[rank].capacity = I[rank].capacity;
   }
+  tp[1] = now_s();
   if (bb_team_barrier(mem, 180) != BB_OK && !rc)
     rc = BB_ERR_STATE;
+  tp[2] = now_s();
   if (!rc)
     for (int j = 0; j < world && !rc; j++)
     {
@@ -505,6 +513,7 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
       }
     }
   int best = best0;
+  tp[3] = now_s();
   if (!rc)
   {
     const double w0 = now_s();
@@ -530,6 +539,7 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     else
       bb_engine_get_stats(w.e, &st);
   }
+  tp[4] = now_s();
   I[rank].tree = st.tree + (rank == 0 ? base_tree : 0);
   I[rank].sol = st.sol + (rank == 0 ? base_sol : 0);
   I[rank].steals = tr.steals;
@@ -582,9 +592,16 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
       if (opened[j][2 + s])
         cudaIpcCloseMemHandle(w.peers[j].tailw[s]);
     }
+  tp[5] = now_s();
   bb_team_barrier(mem, 60); /* every mapping of our pool is closed before we free it */
   if (w.e)
     bb_engine_destroy(w.e);
+  tp[6] = now_s();
+  if (trace)
+    fprintf(stderr, "[bb rank %d] create+handles %.1f ms, barrier %.1f, ipc open %.1f, warm-up..search end %.1f "
+                    "(search %.1f), reduce+close %.1f, destroy %.1f\n", rank, (tp[1] - tp[0]) * 1e3,
+            (tp[2] - tp[1]) * 1e3, (tp[3] - tp[2]) * 1e3, (tp[4] - tp[3]) * 1e3, search_s * 1e3, (tp[5] - tp[4]) * 1e3,
+            (tp[6] - tp[5]) * 1e3);
   if (mine)
     *mine = st;
   munmap(mem, total);

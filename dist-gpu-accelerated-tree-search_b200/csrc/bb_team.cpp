@@ -345,10 +345,10 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
       const double dt = now_ms() - t0;
       me_s.busy_ms += ms;
       if (D > 1)
-      { /* poll often enough to answer thieves within a few milliseconds */
-        if (dt > 4.0 && k > 1)
+      { /* poll often enough to answer thieves within about a millisecond */
+        if (dt > 1.5 && k > 1)
           k /= 2;
-        else if (dt < 1.0 && k < kmax)
+        else if (dt < 0.4 && k < kmax)
           k *= 2;
       }
       if (b < w.best)
