@@ -51,7 +51,7 @@ class PfspInstance(C.Structure):
 class Config(C.Structure):
     _fields_ = [("device", C.c_int), ("M", C.c_int), ("m", C.c_int), ("capacity", C.c_longlong),
                 ("iters_per_launch", C.c_int), ("lb2_prefilter", C.c_int), ("lb2_staged", C.c_int),
-                ("lb2_stage_a", C.c_int), ("lb2_table", C.c_int)]
+                ("lb2_stage_a", C.c_int), ("lb2_table", C.c_int), ("packed", C.c_int)]
 
 
 class Stats(C.Structure):

@@ -12,6 +12,7 @@
 #include "bb_nq_kernels.cuh"
 #include "bb_pfsp_kernels.cuh"
 #include "bb_pfsp_lb2.cuh"
+#include "bb_pfsp_packed.cuh"
 
 #include <climits>
 #include <cstdarg>
@@ -77,6 +78,7 @@ struct bb_engine
   void *table_mem;
   int lb, n, m, prefilter;
   int table;           /* LB2: subset-table kernel (pfsp_expand<3,MM>) */
+  int packed;          /* LB1_d / LB1 / LB2-table: two-children-per-lane kernel (bb_pfsp_packed.cuh) */
   void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
@@ -109,6 +111,7 @@ extern "C" void bb_config_default(bb_config *cfg)
   cfg->lb2_staged = 1;
   cfg->lb2_stage_a = 8;
   cfg->lb2_table = 1;
+  cfg->packed = 1;
 }
 
 /* ------------------------------------------------------------------ small kernels: plan / seed / export */
@@ -454,6 +457,22 @@ static const void *pick_pfsp_kernel(int mm)
   }
 }
 
+template <int LB>
+static const void *pick_pfsp_kernel2(int mm)
+{
+  switch (mm)
+  {
+  case 5:
+    return (const void *)bbk::pfsp_expand2<LB, 5>;
+  case 10:
+    return (const void *)bbk::pfsp_expand2<LB, 10>;
+  case 20:
+    return (const void *)bbk::pfsp_expand2<LB, 20>;
+  default:
+    return (const void *)bbk::pfsp_expand2<LB, 0>;
+  }
+}
+
 static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
 {
   const int n = ins->nb_jobs, m = ins->nb_machines, P = ins->nb_machine_pairs;
@@ -521,6 +540,8 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   e->T.score = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + sz_ord);
   e->T.hist = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + 2 * sz_ord);
   e->T.best_known = ins->best_known;
+  for (int k = 0; k < BB_MAX_MACHINES; k++)
+    e->T.tails2[k] = k < m ? (uint32_t)ins->min_tails[k] * 0x10001u : 0u;
   return BB_OK;
 }
 
@@ -531,6 +552,7 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
   e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
+  e->packed = cfg ? (cfg->packed != 0) : 1;
   e->table = (lb == 2) && (cfg ? (cfg->lb2_table != 0) : 1) && ins->nb_machine_pairs > 0;
   e->staged = (lb == 2) && !e->table && (cfg ? (cfg->lb2_staged != 0) : 1) && ins->nb_machine_pairs > 0;
   e->stage_a = cfg && cfg->lb2_stage_a > 0 ? cfg->lb2_stage_a : 8;
@@ -557,7 +579,8 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
     BB_CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->T.g16 = (const uint16_t *)e->g16_mem;
     e->T.grow = grow;
-    rc = setup_launch(e, pick_pfsp_kernel<3>(mm), bbk::pfsp_layout(e->m, e->T.P, 3).total);
+    rc = setup_launch(e, e->packed ? pick_pfsp_kernel2<3>(mm) : pick_pfsp_kernel<3>(mm),
+                      bbk::pfsp_layout(e->m, e->T.P, 3).total);
     if (rc)
       return rc;
     return build_graph(e);
@@ -573,7 +596,9 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
       return rc;
     return build_graph(e);
   }
-  const void *k = lb == 0 ? pick_pfsp_kernel<0>(mm) : lb == 1 ? pick_pfsp_kernel<1>(mm) : pick_pfsp_kernel<2>(mm);
+  const void *k = lb == 0   ? (e->packed ? pick_pfsp_kernel2<0>(mm) : pick_pfsp_kernel<0>(mm))
+                  : lb == 1 ? (e->packed ? pick_pfsp_kernel2<1>(mm) : pick_pfsp_kernel<1>(mm))
+                            : pick_pfsp_kernel<2>(mm);
   const int smem = bbk::pfsp_layout(e->m, e->T.P, lb).total;
   rc = setup_launch(e, k, smem);
   if (rc)

@@ -93,6 +93,9 @@ struct bb_pfsp_dev
    * head-independent part of the pair's Johnson makespan on the unscheduled set U, plus min_tails[b] */
   const uint16_t *g16;
   int grow; /* u16 per row (m - 1 rounded up to a multiple of 8) */
+  /* packed kernel (bb_pfsp_packed.cuh): min_tails[i] in both 16-bit halves; lives in the kernel parameter block, so
+   * the unrolled machine loop reads it as a constant-bank operand */
+  uint32_t tails2[BB_MAX_MACHINES];
   int best_known;
 };
 
