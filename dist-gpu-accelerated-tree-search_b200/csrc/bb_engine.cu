@@ -347,7 +347,7 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   if (capacity <= 0)
   {
     /* depth-first batches of M leave up to M*(branching-1) nodes behind per level; measured high-water marks are
-     * 20-75 x M nodes over both stacks. Size each stack to 4 GiB of records (but at least 16 x M nodes), within a
+     * 20-75 x M nodes over both stacks. Size each stack to 4 GiB of records (but at least 48 x M nodes), within a
      * third of the free HBM: pool size drives cudaMalloc / cudaFree / IPC-mapping time, which is most of the
      * set-up cost of a short search, and the planner shrinks batches instead of overflowing near capacity. */
     size_t free_b = 0, total_b = 0;
@@ -355,8 +355,8 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
     const long long rec = (long long)nplanes * 16 + (long long)tail_words * 4;
     const long long by_mem = (long long)(free_b / 3) / (2 * rec);
     capacity = (4ll << 30) / rec;
-    if (capacity < (long long)e->M * 16)
-      capacity = (long long)e->M * 16;
+    if (capacity < (long long)e->M * 48) /* the planner reserves room for maxkids children per popped parent */
+      capacity = (long long)e->M * 48;
     if (capacity < (1 << 22))
       capacity = 1 << 22;
     if (capacity > by_mem)
@@ -580,7 +580,7 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
     e->T.g16 = (const uint16_t *)e->g16_mem;
     e->T.grow = grow;
     rc = setup_launch(e, e->packed ? pick_pfsp_kernel2<3>(mm) : pick_pfsp_kernel<3>(mm),
-                      bbk::pfsp_layout(e->m, e->T.P, 3).total);
+                      bbk::pfsp_layout(e->m, e->T.P, 3, e->packed ? 2 : 1).total);
     if (rc)
       return rc;
     return build_graph(e);
@@ -599,7 +599,7 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   const void *k = lb == 0   ? (e->packed ? pick_pfsp_kernel2<0>(mm) : pick_pfsp_kernel<0>(mm))
                   : lb == 1 ? (e->packed ? pick_pfsp_kernel2<1>(mm) : pick_pfsp_kernel<1>(mm))
                             : pick_pfsp_kernel<2>(mm);
-  const int smem = bbk::pfsp_layout(e->m, e->T.P, lb).total;
+  const int smem = bbk::pfsp_layout(e->m, e->T.P, lb, (e->packed && lb != 2) ? 2 : 1).total;
   rc = setup_launch(e, k, smem);
   if (rc)
     return rc;

@@ -81,7 +81,8 @@ struct pfsp_smem_layout
       off_fc, off_fr, total;
 };
 
-__host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb)
+/* tile_buffers: 1 for the first-generation kernel, 2 for the packed kernel (it prefetches the next tile) */
+__host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb, int tile_buffers = 1)
 {
   pfsp_smem_layout L;
   int o = 0;
@@ -105,7 +106,7 @@ __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb)
   L.off_warp = o;
   int w = 0;
   L.off_tile = w;
-  w += pfsp_planes(m) * BB_TILE_MAX * 16;
+  w += tile_buffers * pfsp_planes(m) * BB_TILE_MAX * 16;
   L.off_offs = w;
   w += 36 * 4;
   L.off_surv = w; /* survivors of the tile: (parent << 8) | slot, at most 32 parents x BB_MAX_JOBS children */

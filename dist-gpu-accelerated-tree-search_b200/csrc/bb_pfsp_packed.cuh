@@ -28,8 +28,12 @@
 namespace bbk
 {
 
+#ifndef BB_PACKED_MIN_CTAS
+#define BB_PACKED_MIN_CTAS 2
+#endif
+
 template <int LB, int MM>
-__global__ void __launch_bounds__(BB_CTA_THREADS, (LB == 3 ? 2 : 3))
+__global__ void __launch_bounds__(BB_CTA_THREADS, (LB == 3 ? 2 : BB_PACKED_MIN_CTAS))
 pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T, const int prefilter)
 {
   static_assert(LB == 0 || LB == 1 || LB == 3, "packed kernel: LB1_d, LB1, LB2 through the subset table");
@@ -47,10 +51,10 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
   extern __shared__ __align__(16) unsigned char smem[];
-  const pfsp_smem_layout L = pfsp_layout(m, P, LB);
+  const pfsp_smem_layout L = pfsp_layout(m, P, LB, 2);
   uint8_t *p8 = smem + L.off_p8;
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
-  uint4 *tile_s = reinterpret_cast<uint4 *>(wbase + L.off_tile);       /* [plane][32] */
+  uint4 *tile_buf = reinterpret_cast<uint4 *>(wbase + L.off_tile);     /* 2 x [plane][32] */
   int *offs_s = reinterpret_cast<int *>(wbase + L.off_offs);           /* [33] exclusive lane-slot offsets */
   uint16_t *surv_s = reinterpret_cast<uint16_t *>(wbase + L.off_surv); /* survivors of the tile */
 
@@ -64,20 +68,43 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0}; /* tree, sol, parents, evals, lb2_evals, lb2_pairs */
 
   const int ntiles = (nbatch + TS - 1) / TS;
-  for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += gridDim.x * BB_WARPS_PER_CTA)
+  const int tstride = gridDim.x * BB_WARPS_PER_CTA;
+  /* coalesced asynchronous copy of one tile's parent planes (lane = parent) into a tile buffer: the NEXT tile is
+   * in flight (LDGSTS) while the current one is bounded, so its HBM latency is off the critical path */
+  auto fetch_tile = [&](int tile, uint4 *dstbuf) {
+    if (tile < ntiles)
+    {
+      const int first = tile * TS;
+      if (lane < min(TS, nbatch - first))
+      {
+        const size_t node = (size_t)base + first + lane;
+#pragma unroll
+        for (int q = 0; q < NPL; q++)
+        {
+          const unsigned sa = (unsigned)__cvta_generic_to_shared(dstbuf + q * 32 + lane);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(splanes + (size_t)q * cap + node)
+                       : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int buf = 0;
+  fetch_tile(blockIdx.x * BB_WARPS_PER_CTA + warp, tile_buf);
+  for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += tstride)
   {
+    uint4 *tile_s = tile_buf + buf * (NPL * 32);
+    fetch_tile(tile + tstride, tile_buf + (buf ^ 1) * (NPL * 32));
+    buf ^= 1;
+    asm volatile("cp.async.wait_group 1;" ::: "memory"); /* everything but the prefetch just issued has landed */
+    __syncwarp();
     const int best = *reinterpret_cast<volatile int *>(&ctrl->best);
     const int first = tile * TS;
     const int cnt = min(TS, nbatch - first);
 
-    /* ---- coalesced load of the parents' planes into the warp tile ---- */
     int kids = 0;
     if (lane < cnt)
     {
-      const size_t node = (size_t)base + first + lane;
-#pragma unroll
-      for (int q = 0; q < NPL; q++)
-        tile_s[q * 32 + lane] = splanes[(size_t)q * cap + node];
       const uint32_t w5 = reinterpret_cast<const uint32_t *>(&tile_s[32 + lane])[1];
       kids = n - (int)(w5 & 0xffu);
     }
@@ -213,13 +240,9 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
         cnt6[0] += nsurv;
       }
-      pos = __shfl_sync(0xffffffffu, pos, 0);
-      if (pos + (unsigned)nsurv > (unsigned)cap)
+      /* the cursor value is first needed at the stores below: the child records are built while the atomic is in
+       * flight */
       {
-        if (lane == 0)
-          atomicExch(&ctrl->error, 1);
-      }
-      else
         for (int i0 = 0; i0 < nsurv; i0 += 32)
         {
           const int i = i0 + lane;
@@ -278,15 +301,23 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
 #pragma unroll
             for (int wi = 6 + MP; wi < NPL * 4; wi++)
               w[wi] = 0u;
-            const size_t slot = (size_t)pos + i;
+            const unsigned at = __shfl_sync(__activemask(), pos, 0);
+            if (at + (unsigned)nsurv > (unsigned)cap)
+              atomicExch(&ctrl->error, 1);
+            else
+            {
+              const size_t slot = (size_t)at + i;
 #pragma unroll
-            for (int q = 0; q < NPL; q++)
-              dplanes[(size_t)q * cap + slot] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+              for (int q = 0; q < NPL; q++)
+                dplanes[(size_t)q * cap + slot] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+            }
           }
         }
+      }
     }
     __syncwarp();
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 
   finish_iteration(ctrl, cnt6, src, base, cap);
 }
