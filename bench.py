@@ -406,7 +406,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="pfsp:21:2")
-    ap.add_argument("--M", type=int, default=1 << 20, help="max parents per device iteration (-M)")
+    ap.add_argument("--M", type=int, default=0,
+                    help="max parents per device iteration (-M); 0 = 2 M (PFSP) / 4 M (N-Queens) on one GPU, half of "
+                         "that per GPU on several")
     ap.add_argument("--ref-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lb2-pairloop", action="store_true",
@@ -415,6 +417,8 @@ def main():
     w = parse_workload(args.workload)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.M <= 0:
+        args.M = (1 << 21 if w[0] == "pfsp" else 1 << 22) >> (1 if world > 1 else 0)
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":

@@ -615,8 +615,13 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
   int rc = alloc_common(e, cfg, 1, tw);
   if (rc)
     return rc;
-  const void *k = tw == 0 ? (const void *)bbk::nq_expand<0>
-                  : tw == 1 ? (const void *)bbk::nq_expand<1> : (const void *)bbk::nq_expand<2>;
+  const bool gen2 = cfg ? (cfg->packed != 0) : true; /* `packed` selects the second-generation kernels */
+  const void *k = gen2 ? (tw == 0   ? (const void *)bbk::nq_expand2<0>
+                          : tw == 1 ? (const void *)bbk::nq_expand2<1>
+                                    : (const void *)bbk::nq_expand2<2>)
+                       : (tw == 0   ? (const void *)bbk::nq_expand<0>
+                          : tw == 1 ? (const void *)bbk::nq_expand<1>
+                                    : (const void *)bbk::nq_expand<2>);
   rc = setup_launch(e, k, 0);
   if (rc)
     return rc;

@@ -83,13 +83,54 @@ struct peer_view
   long long capacity;
 };
 
+struct ipc_slot
+{
+  cudaIpcMemHandle_t planes[2];
+  cudaIpcMemHandle_t tailw[2];
+  int has_tail;
+  long long capacity;
+  /* results */
+  unsigned long long tree, sol, steals, steals_ok, donated, warm_tree, warm_sol;
+  double kernel_ms, search_s, warm_s, setup_s;
+  int best, rc;
+};
+
 struct gpu_worker
 {
   bb_engine *e;
   int me;
   double kernel_ms_seen;
   peer_view peers[64];
+  /* one process per GPU: a peer's pool is mapped (cudaIpcOpenMemHandle) the first time we steal from it - mapping
+   * a multi-GB pool costs milliseconds and most peers are never stolen from */
+  const ipc_slot *ipc;
+  bool opened[64][4];
 };
+
+int ensure_peer_mapped(gpu_worker *w, int j)
+{
+  if (!w->ipc || w->peers[j].planes[0])
+    return BB_OK;
+  const ipc_slot &I = w->ipc[j];
+  w->peers[j].capacity = I.capacity;
+  for (int s = 0; s < 2; s++)
+  {
+    cudaError_t err = cudaIpcOpenMemHandle(&w->peers[j].planes[s], I.planes[s], cudaIpcMemLazyEnablePeerAccess);
+    if (err == cudaSuccess)
+    {
+      w->opened[j][s] = true;
+      if (I.has_tail)
+      {
+        err = cudaIpcOpenMemHandle(&w->peers[j].tailw[s], I.tailw[s], cudaIpcMemLazyEnablePeerAccess);
+        if (err == cudaSuccess)
+          w->opened[j][2 + s] = true;
+      }
+    }
+    if (err != cudaSuccess)
+      return bb_fail_cuda(err, "cudaIpcOpenMemHandle", __FILE__, __LINE__);
+  }
+  return BB_OK;
+}
 
 int op_run(void *self, long long max_iters, long long *pool_size, int *best, double *busy_ms)
 {
@@ -115,6 +156,9 @@ int op_donate_done(void *self, int stack) { return bb_engine_donate_done(static_
 int op_pull(void *self, int victim, int stack, long long start, long long count)
 {
   gpu_worker *w = static_cast<gpu_worker *>(self);
+  const int rc = ensure_peer_mapped(w, victim);
+  if (rc)
+    return rc;
   const peer_view &p = w->peers[victim];
   return bb_engine_pull(w->e, p.planes[stack], p.tailw[stack], p.capacity, start, count);
 }
@@ -397,17 +441,6 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
 namespace
 {
 
-struct ipc_slot
-{
-  cudaIpcMemHandle_t planes[2];
-  cudaIpcMemHandle_t tailw[2];
-  int has_tail;
-  long long capacity;
-  /* results */
-  unsigned long long tree, sol, steals, steals_ok, donated, warm_tree, warm_sol;
-  double kernel_ms, search_s, warm_s, setup_s;
-  int best, rc;
-};
 
 int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N, int G, int rank, int world,
                 const char *shm_name, int ws, const bb_config *cfg, bb_search_result *res, bb_stats *mine)
@@ -450,8 +483,6 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   memset(&tr, 0, sizeof(tr));
   unsigned long long base_tree = 0, base_sol = 0;
   double search_s = 0;
-  bool opened[64][4];
-  memset(opened, 0, sizeof(opened));
   auto fail = [&](int code) {
     rc = code;
     bb_team_fail(mem);
@@ -489,29 +520,7 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   if (bb_team_barrier(mem, 180) != BB_OK && !rc)
     rc = BB_ERR_STATE;
   tp[2] = now_s();
-  if (!rc)
-    for (int j = 0; j < world && !rc; j++)
-    {
-      if (j == rank)
-        continue;
-      w.peers[j].capacity = I[j].capacity;
-      for (int s = 0; s < 2 && !rc; s++)
-      {
-        cudaError_t err = cudaIpcOpenMemHandle(&w.peers[j].planes[s], I[j].planes[s], cudaIpcMemLazyEnablePeerAccess);
-        if (err == cudaSuccess)
-        {
-          opened[j][s] = true;
-          if (I[j].has_tail)
-          {
-            err = cudaIpcOpenMemHandle(&w.peers[j].tailw[s], I[j].tailw[s], cudaIpcMemLazyEnablePeerAccess);
-            if (err == cudaSuccess)
-              opened[j][2 + s] = true;
-          }
-        }
-        if (err != cudaSuccess)
-          fail(bb_fail_cuda(err, "cudaIpcOpenMemHandle", __FILE__, __LINE__));
-      }
-    }
+  w.ipc = I; /* peers are mapped lazily, at the first steal (ensure_peer_mapped) */
   int best = best0;
   tp[3] = now_s();
   if (!rc)
@@ -587,9 +596,9 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   for (int j = 0; j < world; j++)
     for (int s = 0; s < 2; s++)
     {
-      if (opened[j][s])
+      if (w.opened[j][s])
         cudaIpcCloseMemHandle(w.peers[j].planes[s]);
-      if (opened[j][2 + s])
+      if (w.opened[j][2 + s])
         cudaIpcCloseMemHandle(w.peers[j].tailw[s]);
     }
   tp[5] = now_s();

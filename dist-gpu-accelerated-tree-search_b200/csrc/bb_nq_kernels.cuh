@@ -202,5 +202,190 @@ nq_expand(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int
   finish_iteration(ctrl, cnt6, src, base, cap);
 }
 
+/*
+ * Second-generation N-Queens kernel: no per-candidate pass at all. The lane that owns a parent derives, from the
+ * placed queens, the SET of safe rows for the next column as one bit mask
+ *     free = ~(rows used | rows hit by a diagonal | rows hit by an anti-diagonal) & ((1 << N) - 1)
+ * (the same test as isSafe, nqueens_c.c:80-96, for all candidate rows at once: a queen (i, b) attacks row
+ * b + (depth - i) and row b - (depth - i) of column depth). popcount(free) is the number of children, so
+ * exploredTree / exploredSol need no enumeration, the tile's survivors are known after one warp scan, ONE cursor
+ * reservation is made per tile, and pass 2 writes child j of parent p as "the j-th set bit of free_p". -g repeats the
+ * derivation of `free` G times behind an opaque register barrier (the work scales with G as the reference's knob
+ * intends). Labels, counts and children are the reference's.
+ */
+template <int TW>
+__global__ void __launch_bounds__(BB_CTA_THREADS, 4)
+nq_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+{
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int cap = pool.capacity;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base, TS = ctrl->tile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int dbyte = TW ? 16 + (N - 16) : 15; /* where depth lives in the 16 + 4*TW byte record */
+  const uint32_t full = (N >= 32) ? 0xffffffffu : ((1u << N) - 1u);
+
+  /* per warp, double buffered (the next tile is copied asynchronously while this one is expanded):
+   * 32 rows of 32 bytes (board bytes 0..23 used); plus offsets [33] and the free masks [32] */
+  __shared__ __align__(16) unsigned char rows_s[BB_WARPS_PER_CTA][2][32 * 32];
+  __shared__ int offs_all[BB_WARPS_PER_CTA][36];
+  __shared__ uint32_t free_all[BB_WARPS_PER_CTA][32];
+  int *offs_s = offs_all[warp];
+  uint32_t *free_s = free_all[warp];
+
+  const uint4 *__restrict__ splane = pool.planes[src];
+  uint4 *__restrict__ dplane = pool.planes[dst];
+  const uint32_t *__restrict__ stail = pool.tailw[src];
+  uint32_t *__restrict__ dtail = pool.tailw[dst];
+
+  unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
+
+  const int ntiles = (nbatch + TS - 1) / TS;
+  const int tstride = gridDim.x * BB_WARPS_PER_CTA;
+  auto fetch_tile = [&](int tile, unsigned char *dstrows) {
+    if (tile < ntiles)
+    {
+      const int first = tile * TS;
+      if (lane < min(TS, nbatch - first))
+      {
+        const size_t node = (size_t)base + first + lane;
+        const unsigned sa = (unsigned)__cvta_generic_to_shared(dstrows + lane * 32);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(splane + node) : "memory");
+#pragma unroll
+        for (int t = 0; t < TW; t++)
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa + 16 + 4 * t), "l"(stail + node * TW + t)
+                       : "memory");
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int buf = 0;
+  fetch_tile(blockIdx.x * BB_WARPS_PER_CTA + warp, rows_s[warp][0]);
+  for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += tstride)
+  {
+    const unsigned char *rows = rows_s[warp][buf];
+    fetch_tile(tile + tstride, rows_s[warp][buf ^ 1]);
+    buf ^= 1;
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    const int first = tile * TS;
+    const int cnt = min(TS, nbatch - first);
+
+    /* ---- per parent: the safe rows of the next column ---- */
+    int kids = 0, cands = 0;
+    uint32_t fr = 0u;
+    bool leaf = false;
+    if (lane < cnt)
+    {
+      const unsigned char *row = rows + lane * 32;
+      const int depth = row[dbyte];
+      leaf = (depth + 1 == N);
+      cands = N - depth;
+      int dd = depth;
+      for (int g = 0; g < G; g++)
+      {
+        asm volatile("" : "+r"(dd)); /* keep the G repetitions as real work, as the reference's -g intends */
+        uint32_t used = 0u;
+        unsigned long long hit = 0ull; /* bit (r + 20): row r is on a diagonal of a placed queen */
+        for (int i = 0; i < dd; i++)
+        {
+          const int b = row[i];
+          const int d = dd - i;
+          used |= 1u << b;
+          hit |= (1ull << (b + d + 20)) | (1ull << (b - d + 20));
+        }
+        fr = ~(used | (uint32_t)(hit >> 20)) & full;
+      }
+      kids = __popc(fr);
+      free_s[lane] = fr;
+    }
+    const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
+    const int incl = warp_incl_scan(wkids, lane);
+    const int nsurv = __shfl_sync(0xffffffffu, incl, 31);
+    offs_s[lane] = incl - wkids;
+    const int allkids = __reduce_add_sync(0xffffffffu, kids);
+    const int allsol = __reduce_add_sync(0xffffffffu, leaf ? kids : 0);
+    const int allcand = __reduce_add_sync(0xffffffffu, cands);
+    if (lane == 0)
+    {
+      offs_s[32] = nsurv;
+      cnt6[0] += allkids; /* exploredTree counts every safe placement, leaves included */
+      cnt6[1] += allsol;
+      cnt6[2] += cnt;
+      cnt6[3] += allcand;
+    }
+    __syncwarp();
+
+    /* ---- one reservation per tile, then every lane writes one child ---- */
+    if (nsurv)
+    {
+      unsigned pos = 0;
+      if (lane == 0)
+        pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
+      for (int i0 = 0; i0 < nsurv; i0 += 32)
+      {
+        const int i = i0 + lane;
+        if (i < nsurv)
+        {
+          int p = 0;
+#pragma unroll
+          for (int st = 16; st > 0; st >>= 1)
+            if (offs_s[p + st] <= i)
+              p += st;
+          const int j = i - offs_s[p];
+          const unsigned char *row = rows + p * 32;
+          const int depth = row[dbyte];
+          uint32_t f = free_s[p];
+          for (int q = 0; q < j; q++) /* j-th safe row */
+            f &= f - 1u;
+          const int r = __ffs(f) - 1;
+          int k = depth; /* where row r sits in the unplaced part of the permutation */
+          while (row[k] != r)
+            k++;
+          uint32_t w[4 + (TW ? TW : 1)];
+          const uint4 q0 = *reinterpret_cast<const uint4 *>(row);
+          w[0] = q0.x;
+          w[1] = q0.y;
+          w[2] = q0.z;
+          w[3] = q0.w;
+#pragma unroll
+          for (int t = 0; t < TW; t++)
+            w[4 + t] = *reinterpret_cast<const uint32_t *>(row + 16 + 4 * t);
+          /* swap board[depth] <-> board[k] (xor patch), then depth+1 (depth byte xor old^new) */
+          const uint32_t x = (uint32_t)(r ^ row[depth]);
+          const uint32_t dx = (uint32_t)(depth ^ (depth + 1));
+#pragma unroll
+          for (int wi = 0; wi < 4 + TW; wi++)
+          {
+            uint32_t patch = 0;
+            if (wi == (depth >> 2))
+              patch ^= x << (8 * (depth & 3));
+            if (wi == (k >> 2))
+              patch ^= x << (8 * (k & 3));
+            if (wi == (dbyte >> 2))
+              patch ^= dx << (8 * (dbyte & 3));
+            w[wi] ^= patch;
+          }
+          const unsigned at = __shfl_sync(__activemask(), pos, 0);
+          if (at + (unsigned)nsurv > (unsigned)cap)
+            atomicExch(&ctrl->error, 1);
+          else
+          {
+            const size_t slot = (size_t)at + i;
+            dplane[slot] = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+            for (int t = 0; t < TW; t++)
+              dtail[slot * TW + t] = w[4 + t];
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  finish_iteration(ctrl, cnt6, src, base, cap);
+}
+
 } // namespace bbk
 #endif

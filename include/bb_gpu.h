@@ -167,8 +167,8 @@ typedef struct bb_config
   int lb2_stage_a;        /* LB2 staged kernel: pairs tried before the survivors are compacted; <=0: 8 */
   int lb2_table;          /* LB2 only: 1 = evaluate LB2 through the per-instance subset table (default; 2^n rows,
                              42 MB at 20x20, built on the device at engine creation), 0 = walk the machine pairs */
-  int packed;             /* PFSP: 1 = second-generation kernel, two sibling children per lane in packed 16-bit
-                             halves (default); 0 = first-generation kernel, one child per lane */
+  int packed;             /* 1 = second-generation kernels (default): PFSP two sibling children per lane in packed
+                             16-bit halves, N-Queens safe-row masks; 0 = first-generation, one child per lane */
 } bb_config;
 
 typedef struct bb_stats
