@@ -73,6 +73,8 @@ struct bb_engine
   bb_pool pool;
   void *pool_mem[2];
   void *tail_mem[2];
+  void *stage_mem;        /* transfer buffer for donations (multi-GPU searches only) */
+  long long stage_nodes;
   /* PFSP */
   bb_pfsp_dev T;
   void *table_mem;
@@ -90,6 +92,11 @@ struct bb_engine
   int threads; /* per CTA */
   int iters_per_launch;
   cudaGraphExec_t graph;
+  cudaGraphExec_t small_graph[5]; /* chains of 1, 2, 4, 8, 16 iterations (built on first use): polling workers */
+  /* pipelined polling (bb_engine_run_pipelined): one batch stays in flight while the host looks at the previous one */
+  bb_ctrl *snap_h;                /* pinned, 2 snapshots of the control block */
+  cudaEvent_t pipe_k0[2], pipe_k1[2], pipe_done[2];
+  int pipe_slot, pipe_inflight;
   cudaEvent_t ev0, ev1, ev_begin, ev_end;
   double kernel_ms, span_ms;
   unsigned long long h2d_bytes, d2h_bytes;
@@ -422,11 +429,11 @@ static int launch_expand(bb_engine *e, cudaStream_t s)
   return BB_OK;
 }
 
-static int build_graph(bb_engine *e)
+static int build_graph_n(bb_engine *e, int iters, cudaGraphExec_t *out)
 {
   cudaGraph_t g;
   BB_CUDA_TRY(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
-  for (int i = 0; i < e->iters_per_launch; i++)
+  for (int i = 0; i < iters; i++)
   {
     int rc = launch_expand(e, e->stream);
     if (rc)
@@ -436,8 +443,38 @@ static int build_graph(bb_engine *e)
     }
   }
   BB_CUDA_TRY(cudaStreamEndCapture(e->stream, &g));
-  BB_CUDA_TRY(cudaGraphInstantiate(&e->graph, g, 0));
+  BB_CUDA_TRY(cudaGraphInstantiate(out, g, 0));
   BB_CUDA_TRY(cudaGraphDestroy(g));
+  return BB_OK;
+}
+
+static int build_graph(bb_engine *e) { return build_graph_n(e, e->iters_per_launch, &e->graph); }
+
+/* enqueue `iters` pool iterations as graph chains: the full chain, then powers of two */
+static int enqueue_iterations(bb_engine *e, long long iters)
+{
+  while (iters > 0)
+  {
+    if (iters >= e->iters_per_launch)
+    {
+      BB_CUDA_TRY(cudaGraphLaunch(e->graph, e->stream));
+      iters -= e->iters_per_launch;
+      e->launches += e->iters_per_launch;
+      continue;
+    }
+    int b = 4;
+    while (b > 0 && ((1 << b) > iters || (1 << b) >= e->iters_per_launch))
+      b--;
+    if (!e->small_graph[b])
+    {
+      const int rc = build_graph_n(e, 1 << b, &e->small_graph[b]);
+      if (rc)
+        return rc;
+    }
+    BB_CUDA_TRY(cudaGraphLaunch(e->small_graph[b], e->stream));
+    iters -= 1 << b;
+    e->launches += 1 << b;
+  }
   return BB_OK;
 }
 
@@ -686,12 +723,27 @@ extern "C" void bb_engine_destroy(bb_engine *e)
     cudaStreamSynchronize(e->stream);
   if (e->graph)
     cudaGraphExecDestroy(e->graph);
+  for (int b = 0; b < 5; b++)
+    if (e->small_graph[b])
+      cudaGraphExecDestroy(e->small_graph[b]);
+  if (e->snap_h)
+  {
+    cudaFreeHost(e->snap_h);
+    for (int s = 0; s < 2; s++)
+    {
+      cudaEventDestroy(e->pipe_k0[s]);
+      cudaEventDestroy(e->pipe_k1[s]);
+      cudaEventDestroy(e->pipe_done[s]);
+    }
+  }
   for (int s = 0; s < 2; s++)
   {
     if (e->pool_mem[s])
       cudaFree(e->pool_mem[s]);
     if (e->tail_mem[s])
       cudaFree(e->tail_mem[s]);
+    if (s == 0 && e->stage_mem)
+      cudaFree(e->stage_mem);
   }
   if (e->table_mem)
     cudaFree(e->table_mem);
@@ -913,24 +965,38 @@ __global__ void k_donate(bb_ctrl *c, int stack, int count, int total_warps)
   if (threadIdx.x == 0 && blockIdx.x == 0)
   {
     c->bot[stack] += count;
-    c->hold[stack] += 1;
     bbk::plan_next(c, c->src, total_warps); /* the planned batch may have reached into the donated range */
   }
 }
 
-__global__ void k_donate_done(bb_ctrl *c, int stack, int total_warps)
+/* Transfer buffer of an engine that takes part in a multi-GPU search: a donation is copied out of the pool into
+ * this buffer (plane-major, compact) and the thief reads the BUFFER, not the pool. Only this small allocation has
+ * to be visible to the peers: mapping a whole multi-GB pool with cudaIpcOpenMemHandle costs ~50 ms per peer
+ * (measured), mapping 128 MB about one. */
+int bb_engine_stage_alloc(bb_engine *e, size_t bytes)
 {
-  if (threadIdx.x == 0 && blockIdx.x == 0)
-  {
-    c->hold[stack] -= 1;
-    bbk::plan_next(c, c->src, total_warps);
-  }
+  ENGINE_SET_DEVICE(e);
+  const long long rec = (long long)e->pool.nplanes * 16 + (long long)e->pool.tail_words * 4;
+  long long nodes = (long long)(bytes / (size_t)rec);
+  if (nodes > e->pool.capacity)
+    nodes = e->pool.capacity;
+  if (nodes < 1024)
+    return bb_fail(BB_ERR_ARG, "transfer buffer of %zu bytes is too small", bytes);
+  BB_CUDA_TRY(cudaMalloc(&e->stage_mem, (size_t)nodes * rec));
+  e->stage_nodes = nodes;
+  return BB_OK;
 }
 
+void *bb_engine_stage_ptr(bb_engine *e) { return e->stage_mem; }
+
+/* victim side: reserve the oldest nodes of the fuller stack (they sit at the bottom: shallow nodes, large
+ * sub-trees) and copy them into the transfer buffer; count = 0 when there is too little to share */
 int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int *stack, long long *start,
                      long long *count)
 {
   *count = 0;
+  if (!e->stage_mem)
+    return bb_fail(BB_ERR_STATE, "bb_engine_donate: no transfer buffer");
   ENGINE_SET_DEVICE(e);
   int rc = fetch_ctrl(e);
   if (rc)
@@ -945,28 +1011,37 @@ int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int 
     give = s == 0 ? a0 : a1;
   if (give > max_count)
     give = max_count;
+  if (give > e->stage_nodes)
+    give = e->stage_nodes;
   if (give <= 0)
     return BB_OK;
+  const long long from = c->bot[s];
   *stack = s;
-  *start = c->bot[s];
+  *start = 0; /* offset inside the transfer buffer */
   *count = give;
+  uint4 *stage = (uint4 *)e->stage_mem;
+  BB_CUDA_TRY(cudaMemcpy2DAsync(stage, (size_t)give * sizeof(uint4), e->pool.planes[s] + from,
+                                (size_t)e->pool.capacity * sizeof(uint4), (size_t)give * sizeof(uint4),
+                                e->pool.nplanes, cudaMemcpyDeviceToDevice, e->stream));
+  if (e->pool.tail_words)
+    BB_CUDA_TRY(cudaMemcpyAsync(stage + (size_t)give * e->pool.nplanes, e->pool.tailw[s] + from * e->pool.tail_words,
+                                (size_t)give * e->pool.tail_words * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
+                                e->stream));
   k_donate<<<1, 1, 0, e->stream>>>(e->ctrl, s, (int)give, e->grid * (e->threads / 32));
   BB_CUDA_TRY(cudaGetLastError());
-  return fetch_ctrl(e);
+  return fetch_ctrl(e); /* synchronises: the buffer is complete before the thief is told about it */
 }
 
 int bb_engine_donate_done(bb_engine *e, int stack)
 {
-  ENGINE_SET_DEVICE(e);
-  k_donate_done<<<1, 1, 0, e->stream>>>(e->ctrl, stack, e->grid * (e->threads / 32));
-  BB_CUDA_TRY(cudaGetLastError());
-  return fetch_ctrl(e);
+  (void)e;
+  (void)stack; /* the donation left the pool when it was copied out; the caller only frees the buffer for reuse */
+  return BB_OK;
 }
 
-/* thief side: copy `count` records starting at `start` out of a peer's stack (plane base, tail-word base and
- * capacity of THAT stack, device pointers valid on this device) onto the top of our stack 0 */
-int bb_engine_pull(bb_engine *e, const void *peer_planes, const void *peer_tailw, long long peer_capacity,
-                   long long start, long long count)
+/* thief side: append `count` records from a peer's transfer buffer (device pointer valid on this device) to the top
+ * of our stack 0 */
+int bb_engine_pull(bb_engine *e, const void *peer_stage, long long count)
 {
   ENGINE_SET_DEVICE(e);
   int rc = fetch_ctrl(e);
@@ -975,28 +1050,17 @@ int bb_engine_pull(bb_engine *e, const void *peer_planes, const void *peer_tailw
   const long long at = e->ctrl_h->size[0];
   if (at + count > e->pool.capacity)
     return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while taking over %lld nodes", e->pool.capacity, count);
-  BB_CUDA_TRY(cudaMemcpy2DAsync(e->pool.planes[0] + at, (size_t)e->pool.capacity * sizeof(uint4),
-                                (const uint4 *)peer_planes + start, (size_t)peer_capacity * sizeof(uint4),
-                                (size_t)count * sizeof(uint4), e->pool.nplanes, cudaMemcpyDeviceToDevice, e->stream));
+  const uint4 *stage = (const uint4 *)peer_stage;
+  BB_CUDA_TRY(cudaMemcpy2DAsync(e->pool.planes[0] + at, (size_t)e->pool.capacity * sizeof(uint4), stage,
+                                (size_t)count * sizeof(uint4), (size_t)count * sizeof(uint4), e->pool.nplanes,
+                                cudaMemcpyDeviceToDevice, e->stream));
   if (e->pool.tail_words)
-    BB_CUDA_TRY(cudaMemcpyAsync(e->pool.tailw[0] + at * e->pool.tail_words,
-                                (const uint32_t *)peer_tailw + start * e->pool.tail_words,
+    BB_CUDA_TRY(cudaMemcpyAsync(e->pool.tailw[0] + at * e->pool.tail_words, stage + (size_t)count * e->pool.nplanes,
                                 (size_t)count * e->pool.tail_words * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
                                 e->stream));
   k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, (int)count, e->grid * (e->threads / 32));
   BB_CUDA_TRY(cudaGetLastError());
   return fetch_ctrl(e);
-}
-
-void bb_engine_pool_info(bb_engine *e, void **planes, void **tailw, long long *capacity, int *device)
-{
-  for (int s = 0; s < 2; s++)
-  {
-    planes[s] = e->pool.planes[s];
-    tailw[s] = e->pool.tailw[s];
-  }
-  *capacity = e->pool.capacity;
-  *device = e->device;
 }
 
 /* zero the search counters but keep the pool (workers other than 0 after the common warm-up) */
@@ -1033,21 +1097,9 @@ extern "C" int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out)
     if (left <= 0)
       break;
     BB_CUDA_TRY(cudaEventRecord(e->ev0, e->stream));
-    if (left >= e->iters_per_launch)
-    {
-      BB_CUDA_TRY(cudaGraphLaunch(e->graph, e->stream));
-      e->launches += e->iters_per_launch;
-    }
-    else
-    {
-      for (long long i = 0; i < left; i++)
-      {
-        rc = launch_expand(e, e->stream);
-        if (rc)
-          return rc;
-      }
-      e->launches += left;
-    }
+    rc = enqueue_iterations(e, left >= e->iters_per_launch ? e->iters_per_launch : left);
+    if (rc)
+      return rc;
     BB_CUDA_TRY(cudaEventRecord(e->ev1, e->stream));
     rc = fetch_ctrl(e);
     if (rc)
@@ -1062,6 +1114,66 @@ extern "C" int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out)
     float ms = 0;
     BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_begin, e->ev_end));
     e->span_ms += ms;
+  }
+  if (out)
+    fill_stats(e, out);
+  if (e->ctrl_h->error)
+    return bb_fail(BB_ERR_OVERFLOW, "device pool overflow: capacity %d nodes per stack is too small (raise "
+                                    "bb_config.capacity or lower M)", e->pool.capacity);
+  return BB_OK;
+}
+
+/* Polling variant for the multi-GPU workers: every call enqueues one more batch of `iters` iterations and returns
+ * the state after the PREVIOUS batch, so the GPU never waits for the host between batches (the device plans its
+ * own iterations; an enqueued batch on an empty pool is a chain of kernels that return at once). The reported pool
+ * size is one batch old; a size of 0 is final. Any other engine call synchronises the stream first. */
+int bb_engine_run_pipelined(bb_engine *e, long long iters, bb_stats *out)
+{
+  ENGINE_SET_DEVICE(e);
+  if (!e->snap_h)
+  {
+    BB_CUDA_TRY(cudaMallocHost(&e->snap_h, 2 * sizeof(bb_ctrl)));
+    for (int s = 0; s < 2; s++)
+    {
+      BB_CUDA_TRY(cudaEventCreate(&e->pipe_k0[s]));
+      BB_CUDA_TRY(cudaEventCreate(&e->pipe_k1[s]));
+      BB_CUDA_TRY(cudaEventCreateWithFlags(&e->pipe_done[s], cudaEventDisableTiming));
+    }
+  }
+  auto enqueue = [&](int slot) -> int {
+    BB_CUDA_TRY(cudaEventRecord(e->pipe_k0[slot], e->stream));
+    const int rc = enqueue_iterations(e, iters);
+    if (rc)
+      return rc;
+    BB_CUDA_TRY(cudaEventRecord(e->pipe_k1[slot], e->stream));
+    BB_CUDA_TRY(cudaMemcpyAsync(&e->snap_h[slot], e->ctrl, sizeof(bb_ctrl), cudaMemcpyDeviceToHost, e->stream));
+    BB_CUDA_TRY(cudaEventRecord(e->pipe_done[slot], e->stream));
+    e->d2h_bytes += sizeof(bb_ctrl);
+    return BB_OK;
+  };
+  int rc;
+  if (!e->pipe_inflight)
+  {
+    if ((rc = enqueue(e->pipe_slot)))
+      return rc;
+    e->pipe_inflight = 1;
+  }
+  const int cur = e->pipe_slot;
+  if ((rc = enqueue(cur ^ 1)))
+    return rc;
+  BB_CUDA_TRY(cudaEventSynchronize(e->pipe_done[cur]));
+  float ms = 0;
+  BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->pipe_k0[cur], e->pipe_k1[cur]));
+  e->kernel_ms += ms;
+  *e->ctrl_h = e->snap_h[cur];
+  e->pipe_slot = cur ^ 1;
+  if (e->ctrl_h->n == 0 || e->ctrl_h->error)
+  { /* the pool was already empty (or failed) after that batch: the batch in flight does nothing */
+    BB_CUDA_TRY(cudaEventSynchronize(e->pipe_done[cur ^ 1]));
+    BB_CUDA_TRY(cudaEventElapsedTime(&ms, e->pipe_k0[cur ^ 1], e->pipe_k1[cur ^ 1]));
+    e->kernel_ms += ms;
+    *e->ctrl_h = e->snap_h[cur ^ 1];
+    e->pipe_inflight = 0;
   }
   if (out)
     fill_stats(e, out);

@@ -12,7 +12,8 @@
  *      not depend on the order in which the device appended the nodes. Worker 0 alone keeps the warm-up counters.
  *   2. parallel phase: bb_team_worker (bb_team.cpp): device iterations, polls, peer-memory work stealing, incumbent
  *      exchange, termination detection. A steal copies node planes from the victim's HBM straight into the thief's
- *      (cudaMemcpy2DAsync on peer-enabled / IPC-mapped pointers: NVLink, no host staging).
+ *      through a small per-GPU transfer buffer (cudaMemcpy2DAsync on peer-enabled / IPC-mapped pointers: NVLink, no host
+ *      staging; only the 128 MB buffers are mapped between processes, not the multi-GB pools).
  *   3. there is no CPU drain step: every pool runs to empty on its GPU.
  */
 #include "bb_internal.cuh"
@@ -34,9 +35,10 @@
 int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int *stack, long long *start,
                      long long *count);
 int bb_engine_donate_done(bb_engine *e, int stack);
-int bb_engine_pull(bb_engine *e, const void *peer_planes, const void *peer_tailw, long long peer_capacity,
-                   long long start, long long count);
-void bb_engine_pool_info(bb_engine *e, void **planes, void **tailw, long long *capacity, int *device);
+int bb_engine_pull(bb_engine *e, const void *peer_stage, long long count);
+int bb_engine_stage_alloc(bb_engine *e, size_t bytes);
+void *bb_engine_stage_ptr(bb_engine *e);
+int bb_engine_run_pipelined(bb_engine *e, long long iters, bb_stats *out);
 
 enum
 {
@@ -76,19 +78,11 @@ struct device_span
   }
 };
 
-struct peer_view
-{
-  void *planes[2];
-  void *tailw[2];
-  long long capacity;
-};
+#define BB_STAGE_BYTES ((size_t)128 << 20) /* transfer buffer per GPU: the most one steal can move */
 
 struct ipc_slot
 {
-  cudaIpcMemHandle_t planes[2];
-  cudaIpcMemHandle_t tailw[2];
-  int has_tail;
-  long long capacity;
+  cudaIpcMemHandle_t stage; /* the rank's transfer buffer */
   /* results */
   unsigned long long tree, sol, steals, steals_ok, donated, warm_tree, warm_sol;
   double kernel_ms, search_s, warm_s, setup_s;
@@ -100,35 +94,20 @@ struct gpu_worker
   bb_engine *e;
   int me;
   double kernel_ms_seen;
-  peer_view peers[64];
-  /* one process per GPU: a peer's pool is mapped (cudaIpcOpenMemHandle) the first time we steal from it - mapping
-   * a multi-GB pool costs milliseconds and most peers are never stolen from */
+  void *peer_stage[64]; /* peers' transfer buffers as seen from this device */
+  /* one process per GPU: a peer's buffer is mapped (cudaIpcOpenMemHandle) the first time we steal from it */
   const ipc_slot *ipc;
-  bool opened[64][4];
+  bool opened[64];
 };
 
 int ensure_peer_mapped(gpu_worker *w, int j)
 {
-  if (!w->ipc || w->peers[j].planes[0])
+  if (!w->ipc || w->peer_stage[j])
     return BB_OK;
-  const ipc_slot &I = w->ipc[j];
-  w->peers[j].capacity = I.capacity;
-  for (int s = 0; s < 2; s++)
-  {
-    cudaError_t err = cudaIpcOpenMemHandle(&w->peers[j].planes[s], I.planes[s], cudaIpcMemLazyEnablePeerAccess);
-    if (err == cudaSuccess)
-    {
-      w->opened[j][s] = true;
-      if (I.has_tail)
-      {
-        err = cudaIpcOpenMemHandle(&w->peers[j].tailw[s], I.tailw[s], cudaIpcMemLazyEnablePeerAccess);
-        if (err == cudaSuccess)
-          w->opened[j][2 + s] = true;
-      }
-    }
-    if (err != cudaSuccess)
-      return bb_fail_cuda(err, "cudaIpcOpenMemHandle", __FILE__, __LINE__);
-  }
+  const cudaError_t err = cudaIpcOpenMemHandle(&w->peer_stage[j], w->ipc[j].stage, cudaIpcMemLazyEnablePeerAccess);
+  if (err != cudaSuccess)
+    return bb_fail_cuda(err, "cudaIpcOpenMemHandle", __FILE__, __LINE__);
+  w->opened[j] = true;
   return BB_OK;
 }
 
@@ -136,7 +115,8 @@ int op_run(void *self, long long max_iters, long long *pool_size, int *best, dou
 {
   gpu_worker *w = static_cast<gpu_worker *>(self);
   bb_stats st;
-  const int rc = bb_engine_run(w->e, max_iters, &st);
+  static const bool no_pipeline = getenv("BB_NO_PIPELINE") != nullptr; /* debugging aid */
+  const int rc = no_pipeline ? bb_engine_run(w->e, max_iters, &st) : bb_engine_run_pipelined(w->e, max_iters, &st);
   if (rc)
     return rc;
   *pool_size = st.pool_size;
@@ -156,11 +136,12 @@ int op_donate_done(void *self, int stack) { return bb_engine_donate_done(static_
 int op_pull(void *self, int victim, int stack, long long start, long long count)
 {
   gpu_worker *w = static_cast<gpu_worker *>(self);
+  (void)stack;
+  (void)start; /* the donation sits at the beginning of the victim's transfer buffer */
   const int rc = ensure_peer_mapped(w, victim);
   if (rc)
     return rc;
-  const peer_view &p = w->peers[victim];
-  return bb_engine_pull(w->e, p.planes[stack], p.tailw[stack], p.capacity, start, count);
+  return bb_engine_pull(w->e, w->peer_stage[victim], count);
 }
 
 int op_set_best(void *self, int best) { return bb_engine_set_best(static_cast<gpu_worker *>(self)->e, best); }
@@ -352,9 +333,11 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       };
       const double c0 = now_s();
       w.e = create_engine(kind, ins, lb, N, G, &c, i);
-      o.setup_s = now_s() - c0;
       if (!w.e)
         fail(BB_ERR_CUDA);
+      else if (bb_engine_stage_alloc(w.e, BB_STAGE_BYTES) != BB_OK)
+        fail(BB_ERR_CUDA);
+      o.setup_s = now_s() - c0;
       if (bb_team_barrier(team, 120) != BB_OK || o.rc)
       {
         if (w.e)
@@ -364,10 +347,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         return;
       }
       for (int j = 0; j < D; j++)
-      {
-        int dev;
-        bb_engine_pool_info(W[j].e, w.peers[j].planes, w.peers[j].tailw, &w.peers[j].capacity, &dev);
-      }
+        w.peer_stage[j] = bb_engine_stage_ptr(W[j].e); /* peer access is enabled: direct pointers */
       int best = best0;
       const double w0 = now_s();
       int rc = seed_partition(w.e, kind, D, i, m_keep, best0, &o.base_tree, &o.base_sol, &best);
@@ -496,31 +476,20 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     if (!w.e)
       fail(BB_ERR_CUDA);
   }
+  if (!rc && bb_engine_stage_alloc(w.e, BB_STAGE_BYTES) != BB_OK)
+    fail(BB_ERR_CUDA);
   if (!rc)
   {
-    void *pl[2], *tw[2];
-    int dev;
-    bb_engine_pool_info(w.e, pl, tw, &I[rank].capacity, &dev);
-    I[rank].has_tail = tw[0] != nullptr;
-    for (int s = 0; s < 2 && !rc; s++)
-    {
-      cudaError_t err = cudaIpcGetMemHandle(&I[rank].planes[s], pl[s]);
-      if (err == cudaSuccess && tw[s])
-        err = cudaIpcGetMemHandle(&I[rank].tailw[s], tw[s]);
-      if (err != cudaSuccess)
-        fail(bb_fail_cuda(err, "cudaIpcGetMemHandle", __FILE__, __LINE__));
-    }
-    w.peers[rank].planes[0] = pl[0];
-    w.peers[rank].planes[1] = pl[1];
-    w.peers[rank].tailw[0] = tw[0];
-    w.peers[rank].tailw[1] = tw[1];
-    w.peers[rank].capacity = I[rank].capacity;
+    const cudaError_t err = cudaIpcGetMemHandle(&I[rank].stage, bb_engine_stage_ptr(w.e));
+    if (err != cudaSuccess)
+      fail(bb_fail_cuda(err, "cudaIpcGetMemHandle", __FILE__, __LINE__));
+    w.peer_stage[rank] = bb_engine_stage_ptr(w.e);
   }
   tp[1] = now_s();
   if (bb_team_barrier(mem, 180) != BB_OK && !rc)
     rc = BB_ERR_STATE;
   tp[2] = now_s();
-  w.ipc = I; /* peers are mapped lazily, at the first steal (ensure_peer_mapped) */
+  w.ipc = I; /* peers' transfer buffers are mapped lazily, at the first steal (ensure_peer_mapped) */
   int best = best0;
   tp[3] = now_s();
   if (!rc)
@@ -594,13 +563,8 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   else if (!rc)
     rc = BB_ERR_STATE;
   for (int j = 0; j < world; j++)
-    for (int s = 0; s < 2; s++)
-    {
-      if (w.opened[j][s])
-        cudaIpcCloseMemHandle(w.peers[j].planes[s]);
-      if (w.opened[j][2 + s])
-        cudaIpcCloseMemHandle(w.peers[j].tailw[s]);
-    }
+    if (w.opened[j])
+      cudaIpcCloseMemHandle(w.peer_stage[j]);
   tp[5] = now_s();
   bb_team_barrier(mem, 60); /* every mapping of our pool is closed before we free it */
   if (w.e)

@@ -20,6 +20,8 @@
 #include "bb_gpu.h"
 
 #include <limits.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <time.h>
 #include <unistd.h>
@@ -126,7 +128,9 @@ struct worker
     team_slot &thief = S[req - 1];
     int stack = 0;
     long long start = 0, count = 0;
-    if (can_give && !ld(&H->finished))
+    /* one donation at a time: the engine hands work over through a transfer buffer that stays busy until the
+     * thief acknowledges */
+    if (can_give && !ld(&H->finished) && outstanding[0] + outstanding[1] == 0)
     {
       int rc = ops->donate(ops->self, m_keep, max_steal, &stack, &start, &count);
       if (rc)
@@ -330,6 +334,10 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
   long long k = iters_per_poll > 0 ? iters_per_poll : 32;
   const long long kmax = k;
   long long pool = -1;
+  const bool trace = getenv("BB_TRACE_TEAM") != nullptr; /* per-worker time split on stderr */
+  double t_run = 0, t_serve = 0, t_hunt = 0, t_idle = 0;
+  long long n_run = 0, n_hunt = 0, k_sum = 0;
+  const double t_begin = now_ms();
 
   while (!ld(&H->finished) && !ld(&H->failed))
   {
@@ -343,6 +351,9 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
       if (rc)
         break;
       const double dt = now_ms() - t0;
+      t_run += dt;
+      n_run++;
+      k_sum += k;
       me_s.busy_ms += ms;
       if (D > 1)
       { /* poll often enough to answer thieves within about a millisecond */
@@ -355,8 +366,10 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
         w.best = b;
       stll(&me_s.pool_size, pool);
       w.publish_best();
+      const double s0 = now_ms();
       if ((rc = w.adopt_best()) || (rc = w.service_acks()) || (rc = w.service_request(ws != 0)))
         break;
+      t_serve += now_ms() - s0;
       continue;
     }
     /* our pool is empty */
@@ -371,7 +384,11 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
     int got = 0;
     if (ws && D > 1)
     {
-      if ((rc = w.hunt(&got)))
+      const double h0 = now_ms();
+      rc = w.hunt(&got);
+      t_hunt += now_ms() - h0;
+      n_hunt++;
+      if (rc)
         break;
       if (got)
       {
@@ -385,10 +402,17 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
       st(&H->finished, 1);
       break;
     }
+    const double i0 = now_ms();
     nap(D > 1 ? 50 : 1);
+    t_idle += now_ms() - i0;
     if ((rc = w.adopt_best()))
       break;
   }
+  if (trace)
+    fprintf(stderr, "[bb team %d] total %.1f ms: run %.1f ms in %lld calls (avg k %.1f, device busy %.1f ms), serve %.1f, "
+                    "hunt %.1f in %lld rounds, idle naps %.1f; steals %llu/%llu donated %llu\n", me, now_ms() - t_begin,
+            t_run, n_run, n_run ? (double)k_sum / n_run : 0.0, me_s.busy_ms, t_serve, t_hunt, n_hunt, t_idle,
+            me_s.steals_ok, me_s.steals, me_s.donated);
   if (rc)
     st(&H->failed, 1);
   /* leave nobody waiting on us, and keep our memory until every copy out of it is acknowledged */
