@@ -338,6 +338,31 @@ __global__ void k_export_nq(uint8_t *__restrict__ nodes, bb_pool pool, int stack
 
 /* ------------------------------------------------------------------ creation */
 
+/* The node stacks and the LB2 table come from the device's stream-ordered allocator with an unlimited release
+ * threshold: the first engine of a process pays cudaMalloc-class cost for its multi-GB pool, later engines on the
+ * same GPU (one search after another, which is how the library is used) get the cached blocks back in microseconds.
+ * The memory returns to the driver at process exit. */
+static int pool_alloc(bb_engine *e, void **ptr, size_t bytes)
+{
+  static thread_local unsigned long long configured = 0ull; /* bit per device ordinal < 64 */
+  if (e->device < 64 && !((configured >> e->device) & 1ull))
+  {
+    cudaMemPool_t mp;
+    BB_CUDA_TRY(cudaDeviceGetDefaultMemPool(&mp, e->device));
+    unsigned long long keep = ~0ull;
+    BB_CUDA_TRY(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &keep));
+    configured |= 1ull << e->device;
+  }
+  BB_CUDA_TRY(cudaMallocAsync(ptr, bytes, e->stream));
+  return BB_OK;
+}
+
+static void pool_free(bb_engine *e, void *ptr)
+{
+  if (ptr)
+    cudaFreeAsync(ptr, e->stream);
+}
+
 static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tail_words)
 {
   bb_config c;
@@ -354,16 +379,15 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   if (capacity <= 0)
   {
     /* depth-first batches of M leave up to M*(branching-1) nodes behind per level; measured high-water marks are
-     * 20-75 x M nodes over both stacks. Size each stack to 4 GiB of records (but at least 48 x M nodes), within a
-     * third of the free HBM: pool size drives cudaMalloc / cudaFree / IPC-mapping time, which is most of the
-     * set-up cost of a short search, and the planner shrinks batches instead of overflowing near capacity. */
+     * 20-75 x M nodes over both stacks, and the planner keeps room for maxkids children per popped parent. Size each
+     * stack to 48 x M nodes (at least 4 M nodes), within a third of the free HBM: pool size drives allocation /
+     * release / mapping time, which is most of the set-up cost of a short search, and the planner shrinks batches
+     * instead of overflowing near capacity. */
     size_t free_b = 0, total_b = 0;
     BB_CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
     const long long rec = (long long)nplanes * 16 + (long long)tail_words * 4;
     const long long by_mem = (long long)(free_b / 3) / (2 * rec);
-    capacity = (4ll << 30) / rec;
-    if (capacity < (long long)e->M * 48) /* the planner reserves room for maxkids children per popped parent */
-      capacity = (long long)e->M * 48;
+    capacity = (long long)e->M * 48;
     if (capacity < (1 << 22))
       capacity = 1 << 22;
     if (capacity > by_mem)
@@ -386,12 +410,16 @@ static int alloc_common(bb_engine *e, const bb_config *cfg, int nplanes, int tai
   e->pool.tail_words = tail_words;
   for (int s = 0; s < 2; s++)
   {
-    BB_CUDA_TRY(cudaMalloc(&e->pool_mem[s], (size_t)capacity * nplanes * sizeof(uint4)));
+    int rc = pool_alloc(e, &e->pool_mem[s], (size_t)capacity * nplanes * sizeof(uint4));
+    if (rc)
+      return rc;
     e->pool.planes[s] = (uint4 *)e->pool_mem[s];
     e->pool.tailw[s] = nullptr;
     if (tail_words)
     {
-      BB_CUDA_TRY(cudaMalloc(&e->tail_mem[s], (size_t)capacity * tail_words * sizeof(uint32_t)));
+      rc = pool_alloc(e, &e->tail_mem[s], (size_t)capacity * tail_words * sizeof(uint32_t));
+      if (rc)
+        return rc;
       e->pool.tailw[s] = (uint32_t *)e->tail_mem[s];
     }
   }
@@ -606,8 +634,10 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
      * Johnson schedules the reference precomputes on the host) */
     const int grow = ((e->m - 1) + 7) & ~7;
     const size_t rows = (size_t)1 << e->n;
-    BB_CUDA_TRY(cudaMalloc(&e->g16_mem, rows * grow * sizeof(uint16_t)));
-    e->table_bytes += rows * grow * sizeof(uint16_t);
+    rc = pool_alloc(e, &e->g16_mem, rows * grow * sizeof(uint16_t));
+    if (rc)
+      return rc;
+    /* built on the device from the uploaded tables: HBM footprint, not a host-to-device copy */
     const int P = e->T.P;
     const size_t sm = (size_t)P * BB_MAX_JOBS * 12 + (size_t)P * 8 + BB_MAX_MACHINES * 4 + BB_MAX_MACHINES * 256 * 4;
     BB_CUDA_TRY(cudaFuncSetAttribute(k_lb2_build_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
@@ -738,17 +768,16 @@ extern "C" void bb_engine_destroy(bb_engine *e)
   }
   for (int s = 0; s < 2; s++)
   {
-    if (e->pool_mem[s])
-      cudaFree(e->pool_mem[s]);
-    if (e->tail_mem[s])
-      cudaFree(e->tail_mem[s]);
+    pool_free(e, e->pool_mem[s]);
+    pool_free(e, e->tail_mem[s]);
     if (s == 0 && e->stage_mem)
       cudaFree(e->stage_mem);
   }
   if (e->table_mem)
     cudaFree(e->table_mem);
-  if (e->g16_mem)
-    cudaFree(e->g16_mem);
+  pool_free(e, e->g16_mem);
+  if (e->stream)
+    cudaStreamSynchronize(e->stream);
   if (e->ctrl)
     cudaFree(e->ctrl);
   if (e->ctrl_h)

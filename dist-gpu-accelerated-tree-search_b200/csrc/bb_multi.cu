@@ -231,12 +231,23 @@ bb_engine *create_engine(int kind, const bb_pfsp_instance *ins, int lb, int N, i
   else
     bb_config_default(&c);
   c.device = device;
+  if (c.capacity <= 0)
+  {
+    /* a worker of a multi-GPU search holds only its share of the tree: 26 x M nodes per stack keep the planner's
+     * worst-case room (maxkids children per popped parent) and halve the cudaMalloc / cudaFree time, which D
+     * processes pay one after the other (device memory mapping is serialised system-wide) */
+    const long long M = c.M > 0 ? c.M : 50000;
+    c.capacity = 26 * M > (1ll << 22) ? 26 * M : (1ll << 22);
+  }
   return kind == KIND_PFSP ? bb_pfsp_engine_create(ins, lb, &c) : bb_nq_engine_create(N, G, &c);
 }
 
 int search_single(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N, int G, const bb_config *cfg,
                   bb_search_result *res, bb_stats *per_gpu)
 {
+  /* one-time per process and not part of a search: the CUDA context of the device */
+  BB_CUDA_TRY(cudaSetDevice(cfg ? cfg->device : 0));
+  BB_CUDA_TRY(cudaFree(nullptr));
   const double t0 = now_s();
   bb_engine *e = kind == KIND_PFSP ? bb_pfsp_engine_create(ins, lb, cfg) : bb_nq_engine_create(N, G, cfg);
   if (!e)

@@ -223,8 +223,8 @@ typedef struct bb_search_result
   unsigned long long tree;
   unsigned long long sol;
   int best;
-  double elapsed_s;     /* wall time of the call: engine creation, table upload, search, teardown (with D > 1 in one
-                           process the one-time CUDA context creation and peer enabling are not included) */
+  double elapsed_s;     /* wall time of the call: engine creation, table upload, search, teardown; the one-time
+                           CUDA context creation (and peer enabling for D > 1) of the process is not included */
   double kernel_ms_max; /* max over GPUs of device time in expand kernels */
   unsigned long long steals, steals_ok;
   double search_s;      /* max over GPUs of the wall time from the common start barrier (pools seeded, tables

@@ -157,6 +157,17 @@ def test_multi_gpu_threads_same_counts(D):
     assert (res.tree, res.sol) == (171129071, 2279184)
 
 
+@pytest.mark.parametrize("inst,lb,opt", [(14, 2, 1377), (3, 0, 1081), (14, 1, 1377)])
+def test_search_from_infinite_upper_bound_finds_the_optimum(inst, lb, opt):
+    """-u 0 (PFSP_lib.c:234-241): the incumbent starts at INT_MAX and is improved by leaves through the device
+    atomicMin; only the optimum is pinned (node counts depend on the traversal order)"""
+    res, _ = bb.pfsp_search(bb.Instance(inst=inst), lb, best0=INT_MAX, M=1 << 16)
+    assert res.best == opt and res.sol >= 1
+    if _gpu_count() >= 2:  # incumbents are exchanged between the workers (checkBest, pfsp_multigpu_cuda.c:30-50)
+        res, _ = bb.pfsp_search(bb.Instance(inst=inst), lb, best0=INT_MAX, D=2, M=1 << 16)
+        assert res.best == opt
+
+
 def test_custom_instance_generic_kernel_and_unknown_optimum():
     """a 9x7 matrix exercises the runtime-m kernel; start from ub = inf to find the optimum, then both
     implementations must walk the same tree from ub = optimum"""
