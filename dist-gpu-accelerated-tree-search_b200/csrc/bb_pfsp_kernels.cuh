@@ -77,8 +77,8 @@ __host__ __device__ inline int pfsp_planes(int m) { return (6 + pfsp_mp(m) + 3) 
 
 struct pfsp_smem_layout
 {
-  int off_p8, off_tails, off_jbit, off_ja, off_jb, off_pairs, off_warp, warp_bytes, off_tile, off_offs, off_surv,
-      off_fc, off_fr, total;
+  int off_p8, off_tails, off_p2, off_jbit, off_ja, off_jb, off_pairs, off_warp, warp_bytes, off_tile, off_offs,
+      off_surv, off_fc, off_fr, total;
 };
 
 /* tile_buffers: 1 for the first-generation kernel, 2 for the packed kernel (it prefetches the next tile) */
@@ -90,6 +90,11 @@ __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb, in
   o += ((m * BB_MAX_JOBS) + 15) & ~15;
   L.off_tails = o;
   o += ((m * 4) + 15) & ~15;
+  /* packed kernel, one-machine bounds: p[i][a] | p[i][b] << 16 for every job pair (a, b): [m][20][20] u32. Not for
+   * the table LB2 (lb 3): its row reads go through L1, which shares the SM's 228 KB with shared memory */
+  L.off_p2 = o;
+  if (tile_buffers == 2 && lb != 3)
+    o += m * BB_MAX_JOBS * BB_MAX_JOBS * 4;
   L.off_jbit = L.off_ja = L.off_jb = L.off_pairs = o;
   if (lb == 2)
   {

@@ -53,6 +53,7 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   extern __shared__ __align__(16) unsigned char smem[];
   const pfsp_smem_layout L = pfsp_layout(m, P, LB, 2);
   uint8_t *p8 = smem + L.off_p8;
+  uint32_t *p2tab = reinterpret_cast<uint32_t *>(smem + L.off_p2); /* [m][20][20]: both children's times, one load */
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
   uint4 *tile_buf = reinterpret_cast<uint4 *>(wbase + L.off_tile);     /* 2 x [plane][32] */
   int *offs_s = reinterpret_cast<int *>(wbase + L.off_offs);           /* [33] exclusive lane-slot offsets */
@@ -60,6 +61,12 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
 
   for (int i = threadIdx.x; i < (m * BB_MAX_JOBS) / 4; i += BB_CTA_THREADS)
     reinterpret_cast<uint32_t *>(p8)[i] = reinterpret_cast<const uint32_t *>(T.p8)[i];
+  for (int i = threadIdx.x; LB != 3 && i < m * BB_MAX_JOBS * BB_MAX_JOBS; i += BB_CTA_THREADS)
+  {
+    const int mi = i / (BB_MAX_JOBS * BB_MAX_JOBS), ab = i - mi * (BB_MAX_JOBS * BB_MAX_JOBS);
+    const int a = ab / BB_MAX_JOBS, b = ab - a * BB_MAX_JOBS;
+    p2tab[i] = (uint32_t)T.p8[mi * BB_MAX_JOBS + a] | ((uint32_t)T.p8[mi * BB_MAX_JOBS + b] << 16);
+  }
   __syncthreads();
 
   const uint4 *__restrict__ splanes = pool.planes[src];
@@ -112,7 +119,8 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     const int incl = warp_incl_scan(slots, lane);
     const int total = __shfl_sync(0xffffffffu, incl, 31);
     const int allkids = __reduce_add_sync(0xffffffffu, kids);
-    offs_s[lane] = incl - slots;
+    const int myoff = incl - slots; /* first lane slot of the parent this lane loaded (every parent has >= 1) */
+    offs_s[lane] = myoff;
     if (lane == 0)
     {
       offs_s[32] = total;
@@ -127,14 +135,12 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     {
       const int c = c0 + lane;
       const bool act = c < total;
-      int p = 0;
-      if (act)
-      {
-#pragma unroll
-        for (int st = 16; st > 0; st >>= 1)
-          if (offs_s[p + st] <= c)
-            p += st;
-      }
+      /* parent of lane slot c = (number of parents starting at or before c) - 1, from two warp votes instead of a
+       * dependent binary search through shared memory */
+      const unsigned before = __ballot_sync(0xffffffffu, lane < cnt && myoff <= c0);
+      const int rel = myoff - c0;
+      const unsigned starts = __reduce_or_sync(0xffffffffu, (lane < cnt && rel > 0 && rel < 32) ? (1u << rel) : 0u);
+      const int p = act ? __popc(before) - 1 + __popc(starts & ((2u << lane) - 1u)) : 0;
       /* byte b of plane q of parent p sits at tile + q*512 + p*16 + b */
       const unsigned char *rec = reinterpret_cast<const unsigned char *>(tile_s) + p * 16;
       const uint32_t pw5 = *reinterpret_cast<const uint32_t *>(rec + 512 + 4);
@@ -148,6 +154,9 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         return *reinterpret_cast<const uint16_t *>(rec + ((idx * 2) >> 4) * 512 + ((idx * 2) & 15));
       };
 
+      const uint32_t smask = pw5 >> 8, fullmask = (1u << n) - 1u;
+      const uint32_t UA = ~(smask | (1u << job0)) & fullmask, UB = ~(smask | (1u << job1)) & fullmask;
+      const uint32_t *p2row = p2tab + job0 * BB_MAX_JOBS + job1;
       uint32_t sr[MU]; /* front + remain of both children per machine (LB 3 reads them back) */
       uint32_t lb2 = 0u, t2 = 0u, carry2 = 0u;
 #pragma unroll
@@ -158,7 +167,9 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         {
           const uint32_t f2 = rd16(12 + i) * 0x10001u;
           const uint32_t r2 = rd16(12 + MP + i) * 0x10001u;
-          const uint32_t p2 = (uint32_t)p8[i * BB_MAX_JOBS + job0] + ((uint32_t)p8[i * BB_MAX_JOBS + job1] << 16);
+          const uint32_t p2 = LB != 3 ? p2row[i * (BB_MAX_JOBS * BB_MAX_JOBS)]
+                                      : (uint32_t)p8[i * BB_MAX_JOBS + job0] +
+                                            ((uint32_t)p8[i * BB_MAX_JOBS + job1] << 16);
           const uint32_t s2 = i == 0 ? f2 : __vmaxu2(t2, f2);
           t2 = s2 + p2;
           sr[i] = s2 + r2;
@@ -191,8 +202,6 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         const bool candB = prefilter ? keepB : two;
         if (candA || candB)
         {
-          const uint32_t smask = pw5 >> 8, full = (1u << n) - 1u;
-          const uint32_t UA = ~(smask | (1u << job0)) & full, UB = ~(smask | (1u << job1)) & full;
           const uint4 *rowA = reinterpret_cast<const uint4 *>(T.g16 + (size_t)UA * T.grow);
           const uint4 *rowB = reinterpret_cast<const uint4 *>(T.g16 + (size_t)UB * T.grow);
           constexpr int NV = (MU - 1 + 7) / 8; /* uint4 loads per row */
