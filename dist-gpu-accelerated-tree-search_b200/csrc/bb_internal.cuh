@@ -40,7 +40,7 @@ struct __align__(256) bb_ctrl
   /* iteration plan, written by the last CTA of the previous iteration (or by the host when seeding) */
   int size[2];         /* top of each stack: live nodes are [bot, size) */
   int bot[2];          /* bottom of each stack: nodes below were donated to another GPU (oldest nodes go first) */
-  int hold[2];         /* donations from this stack whose transfer is not acknowledged yet (blocks the rewind) */
+  int hold[2];         /* reserved (always 0): donations are copied out of the pool before the thief is told */
   int src;             /* stack this iteration pops from */
   int n;               /* parents in this iteration's batch (0 = nothing to do) */
   int base;            /* index of the first parent of the batch in stack src */
