@@ -286,16 +286,18 @@ nq_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
       for (int g = 0; g < G; g++)
       {
         asm volatile("" : "+r"(dd)); /* keep the G repetitions as real work, as the reference's -g intends */
-        uint32_t used = 0u;
-        unsigned long long hit = 0ull; /* bit (r + 20): row r is on a diagonal of a placed queen */
+        uint32_t used = 0u, hit = 0u; /* hit bit r: row r of column `depth` is on a diagonal of a placed queen */
         for (int i = 0; i < dd; i++)
         {
-          const int b = row[i];
-          const int d = dd - i;
-          used |= 1u << b;
-          hit |= (1ull << (b + d + 20)) | (1ull << (b - d + 20));
+          const uint32_t b = row[i];
+          const uint32_t d = (uint32_t)(dd - i);
+          const uint32_t bit = 1u << b;
+          uint32_t up; /* row b + d; PTX shl gives 0 for counts >= 32 (rows >= N do not matter) */
+          asm("shl.b32 %0, %1, %2;" : "=r"(up) : "r"(1u), "r"(b + d));
+          used |= bit;
+          hit |= up | (bit >> d); /* row b - d falls off the low end when b < d */
         }
-        fr = ~(used | (uint32_t)(hit >> 20)) & full;
+        fr = ~(used | hit) & full;
       }
       kids = __popc(fr);
       free_s[lane] = fr;
