@@ -92,3 +92,36 @@ def test_nqueens_run_prints_reference_counts(tmp_path, golden):
     assert parse_final(r.stdout)[:2] == (856188, 14200)
     assert "Resolution of the 12-Queens instance\n  with 2 safety check(s) per evaluation\n" in r.stdout
     assert "Search on GPU completed" in r.stdout and "Exploration terminated." in r.stdout
+
+
+# ------------------------------------------------------------------ bench.py contract
+
+def _bench(*args):
+    import json
+    import sys
+    from __graft_entry__ import ROOT
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *map(str, args)], capture_output=True, text=True,
+                       timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout  # exactly one JSON line on stdout
+    return json.loads(lines[0])
+
+
+def test_bench_reference_arm_runs_without_a_gpu():
+    """`bench.py --impl reference` times the reference's own CPU code (oracle/_ref) on a bounded sample"""
+    d = _bench("--impl", "reference", "--workload", "pfsp:14:2", "--steps", 1, "--warmup", 0, "--ref-seconds", 1)
+    assert d["impl"] == "reference" and d["metric"] == "explored_nodes_per_sec" and d["value"] > 0
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+
+
+@pytest.mark.gpu
+def test_bench_line_has_the_contract_keys():
+    d = _bench("--workload", "pfsp:14:2", "--steps", 2, "--warmup", 3, "--ref-seconds", 1)
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+        assert k in d, k
+    assert d["config"]["tree_nodes"] == 144639 and d["gpu_launches"] > 0 and d["value"] > 0
+    assert d["roofline"]["bound"] == "hbm" and 0 < d["roofline"]["frac"] < 1.5
+    assert d["e2e"]["h2d_bytes_per_step"] > 0 and d["e2e"]["d2h_bytes_per_step"] > 0
