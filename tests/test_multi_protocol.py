@@ -12,12 +12,12 @@ import team_mock
 NQ = {8: (2056, 92), 9: (8393, 352)}  # nqueens_c.out -N 8 / -N 9 (tests/golden/runs.json holds 8; 9 = OEIS A000170)
 
 
-def run_job(N, lopsided):
+def run_job(N, lopsided, world=2):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = random.randint(20000, 40000)
     tag = f"bbt{os.getpid()}_{random.randint(0, 1 << 30)}"
-    procs = [ctx.Process(target=team_mock.worker_main, args=(r, 2, port, N, tag, lopsided, q)) for r in range(2)]
+    procs = [ctx.Process(target=team_mock.worker_main, args=(r, world, port, N, tag, lopsided, q)) for r in range(world)]
     for p in procs:
         p.start()
     outs = [q.get(timeout=180) for _ in procs]
@@ -42,3 +42,14 @@ def test_idle_rank_steals_from_the_loaded_one():
     (r0, mine0, total), (r1, mine1, _) = outs
     assert (total[0], total[1]) == NQ[9]
     assert mine1[0] > 0 and mine1[2] > 0 and mine1[3] > 0, mine1  # explored, successful steals, nodes pulled
+
+
+@pytest.mark.timeout(300)
+def test_four_ranks_one_loaded():
+    """three idle ranks hunt one loaded rank (and later each other): requests are serialised per victim, donations
+    go one at a time, every rank leaves through the epoch-checked termination, and no node is lost or duplicated"""
+    outs = run_job(9, lopsided=True, world=4)
+    total = outs[0][2]
+    assert (total[0], total[1]) == NQ[9]
+    assert all(o[2] == total for o in outs)
+    assert sum(1 for o in outs[1:] if o[1][0] > 0) >= 2  # at least two of the idle ranks got work
