@@ -34,6 +34,7 @@ KNOWN_TREES = {  # exploredTree with ub = optimum (order independent): tests/gol
     ("pfsp", 14, 0): 2573652, ("pfsp", 14, 1): 2573652, ("pfsp", 14, 2): 144639,
     ("pfsp", 21, 2): 3944527267, ("pfsp", 24, 2): 2173092255, ("pfsp", 29, 2): 9499307,
     ("pfsp", 30, 0): 111887480, ("pfsp", 22, 0): 711291688,
+    ("pfsp", 24, 0): 71876969050, ("pfsp", 24, 1): 71876969050, ("pfsp", 21, 0): 260069628524,
     ("nq", 14): 27358552, ("nq", 15): 171129071, ("nq", 16): 1141190302, ("nq", 17): 8017021931,
 }
 LB_NAME = {0: "LB1_d", 1: "LB1", 2: "LB2"}
