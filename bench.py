@@ -30,13 +30,37 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-KNOWN_TREES = {  # exploredTree with ub = optimum (order independent): tests/golden + runs on the B200 box
-    ("pfsp", 14, 0): 2573652, ("pfsp", 14, 1): 2573652, ("pfsp", 14, 2): 144639,
-    ("pfsp", 21, 2): 3944527267, ("pfsp", 24, 2): 2173092255, ("pfsp", 29, 2): 9499307,
-    ("pfsp", 30, 0): 111887480, ("pfsp", 22, 0): 711291688,
-    ("pfsp", 24, 0): 71876969050, ("pfsp", 24, 1): 71876969050, ("pfsp", 21, 0): 260069628524,
-    ("nq", 14): 27358552, ("nq", 15): 171129071, ("nq", 16): 1141190302, ("nq", 17): 8017021931,
-}
+def known_trees():
+    """exploredTree with ub = optimum (order independent), every value printed by the reference itself:
+    tests/golden/runs.json (reference CPU programs run in the build container, tests/golden/make_golden.py) and
+    tests/golden/ref_gpu_runs.json (the reference's GPU drivers rebuilt for sm_100a and run on the B200 box,
+    scripts/gpu_pin_reference.sh + scripts/pins_to_golden.py)."""
+    out = {}
+    gd = os.path.join(ROOT, "tests", "golden")
+    try:
+        g = json.load(open(os.path.join(gd, "runs.json")))
+        for r in g["pfsp"] + g["survey"]["pfsp"]:
+            if not r.get("predicted") and r.get("ub", 1) == 1:
+                out[("pfsp", r["inst"], r["lb"])] = r["tree"]
+        for r in g["nqueens"] + g["survey"]["nqueens"]:
+            if not r.get("predicted"):
+                out[("nq", r["N"])] = r["tree"]
+    except (OSError, KeyError, ValueError):
+        pass
+    try:
+        g = json.load(open(os.path.join(gd, "ref_gpu_runs.json")))
+        for k, r in g["runs"].items():
+            parts = k.split(":")
+            out[(parts[0],) + tuple(int(x) for x in parts[1:])] = r["tree"]
+    except (OSError, KeyError, ValueError):
+        pass
+    for (kind, *rest), tree in list(out.items()):  # LB1 and LB1_d bound identically (SURVEY section 0)
+        if kind == "pfsp" and rest[1] in (0, 1):
+            out.setdefault(("pfsp", rest[0], 1 - rest[1]), tree)
+    return out
+
+
+KNOWN_TREES = known_trees()
 LB_NAME = {0: "LB1_d", 1: "LB1", 2: "LB2"}
 
 

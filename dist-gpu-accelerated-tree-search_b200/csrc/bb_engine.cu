@@ -13,6 +13,7 @@
 #include "bb_pfsp_kernels.cuh"
 #include "bb_pfsp_lb2.cuh"
 #include "bb_pfsp_packed.cuh"
+#include "bb_pfsp_tpp.cuh"
 
 #include <climits>
 #include <cstdarg>
@@ -80,12 +81,14 @@ struct bb_engine
   void *table_mem;
   int lb, n, m, prefilter;
   int table;           /* LB2: subset-table kernel (pfsp_expand<3,MM>) */
-  int packed;          /* LB1_d / LB1 / LB2-table: two-children-per-lane kernel (bb_pfsp_packed.cuh) */
+  int packed;          /* LB1_d / LB1 / LB2-table: 2 = lane-per-parent kernel (bb_pfsp_tpp.cuh, default), 1 = two
+                          children per lane on the warp tile (bb_pfsp_packed.cuh), 0 = first generation */
   void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
   /* N-Queens */
   int N, G;
+  int nq_gen; /* 3 = masks travel with the node (nq_expand3, 32-byte record), 2 / 1 = earlier kernels (board + depth) */
   /* launch */
   const void *kernel;
   int grid, smem;
@@ -118,7 +121,7 @@ extern "C" void bb_config_default(bb_config *cfg)
   cfg->lb2_staged = 1;
   cfg->lb2_stage_a = 8;
   cfg->lb2_table = 1;
-  cfg->packed = 1;
+  cfg->packed = 2;
 }
 
 /* ------------------------------------------------------------------ small kernels: plan / seed / export */
@@ -336,6 +339,48 @@ __global__ void k_export_nq(uint8_t *__restrict__ nodes, bb_pool pool, int stack
     nd[1 + j] = j < N ? (uint8_t)((ww[j >> 2] >> (8 * (j & 3))) & 0xff) : 0;
 }
 
+/* third-generation N-Queens record (bb_nq_kernels.cuh, nq_expand3): board[20] + used rows | depth << 24 + the rows
+ * of the next column attacked along the two diagonal directions, derived once per seeded node */
+__global__ void k_seed_nq3(const uint8_t *__restrict__ nodes, int count, bb_pool pool, int N, int at)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const uint8_t *nd = nodes + (size_t)i * (1 + BB_MAX_QUEENS);
+  const int depth = nd[0];
+  uint32_t w[5] = {0u, 0u, 0u, 0u, 0u};
+  for (int j = 0; j < N; j++)
+    w[j >> 2] |= (uint32_t)nd[1 + j] << (8 * (j & 3));
+  const uint32_t full = (1u << N) - 1u;
+  uint32_t used = 0u, up = 0u, down = 0u;
+  for (int c = 0; c < depth; c++)
+  {
+    const int b = nd[1 + c], d = depth - c;
+    used |= 1u << b;
+    if (b + d < 32)
+      up |= 1u << (b + d);
+    if (b >= d)
+      down |= 1u << (b - d);
+  }
+  pool.planes[0][at + i] = make_uint4(w[0], w[1], w[2], w[3]);
+  pool.planes[0][(size_t)pool.capacity + at + i] = make_uint4(w[4], (used & full) | ((uint32_t)depth << 24), up & full, down & full);
+}
+
+__global__ void k_export_nq3(uint8_t *__restrict__ nodes, bb_pool pool, int stack, int from, int count, int out_at,
+                             int N)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const uint4 q0 = pool.planes[stack][from + i];
+  const uint4 q1 = pool.planes[stack][(size_t)pool.capacity + from + i];
+  const uint32_t ww[5] = {q0.x, q0.y, q0.z, q0.w, q1.x};
+  uint8_t *nd = nodes + (size_t)(out_at + i) * (1 + BB_MAX_QUEENS);
+  nd[0] = (uint8_t)(q1.y >> 24);
+  for (int j = 0; j < BB_MAX_QUEENS; j++)
+    nd[1 + j] = j < N ? (uint8_t)((ww[j >> 2] >> (8 * (j & 3))) & 0xff) : 0;
+}
+
 /* ------------------------------------------------------------------ creation */
 
 /* The node stacks and the LB2 table come from the device's stream-ordered allocator with an unlimited release
@@ -538,6 +583,22 @@ static const void *pick_pfsp_kernel2(int mm)
   }
 }
 
+template <int LB>
+static const void *pick_pfsp_kernel3(int mm)
+{
+  switch (mm)
+  {
+  case 5:
+    return (const void *)bbk::pfsp_expand3<LB, 5>;
+  case 10:
+    return (const void *)bbk::pfsp_expand3<LB, 10>;
+  case 20:
+    return (const void *)bbk::pfsp_expand3<LB, 20>;
+  default:
+    return (const void *)bbk::pfsp_expand3<LB, 0>;
+  }
+}
+
 static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
 {
   const int n = ins->nb_jobs, m = ins->nb_machines, P = ins->nb_machine_pairs;
@@ -605,6 +666,7 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   e->T.score = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + sz_ord);
   e->T.hist = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + 2 * sz_ord);
   e->T.best_known = ins->best_known;
+  e->T.one = 1u;
   for (int k = 0; k < BB_MAX_MACHINES; k++)
     e->T.tails2[k] = k < m ? (uint32_t)ins->min_tails[k] * 0x10001u : 0u;
   return BB_OK;
@@ -617,7 +679,13 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
   e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
-  e->packed = cfg ? (cfg->packed != 0) : 1;
+  e->packed = cfg ? cfg->packed : 2;
+  if (e->packed < 0 || e->packed > 2)
+    e->packed = 2;
+  /* the lane-per-parent kernel packs two processing times per PRMT with the sign-replicate trick: times <= 127 */
+  for (int i = 0; e->packed == 2 && i < ins->nb_jobs * ins->nb_machines; i++)
+    if (ins->p_times[i] > 127)
+      e->packed = 1;
   e->table = (lb == 2) && (cfg ? (cfg->lb2_table != 0) : 1) && ins->nb_machine_pairs > 0;
   e->staged = (lb == 2) && !e->table && (cfg ? (cfg->lb2_staged != 0) : 1) && ins->nb_machine_pairs > 0;
   e->stage_a = cfg && cfg->lb2_stage_a > 0 ? cfg->lb2_stage_a : 8;
@@ -646,8 +714,11 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
     BB_CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->T.g16 = (const uint16_t *)e->g16_mem;
     e->T.grow = grow;
-    rc = setup_launch(e, e->packed ? pick_pfsp_kernel2<3>(mm) : pick_pfsp_kernel<3>(mm),
-                      bbk::pfsp_layout(e->m, e->T.P, 3, e->packed ? 2 : 1).total);
+    if (e->packed == 2)
+      rc = setup_launch(e, pick_pfsp_kernel3<3>(mm), bbk::tpp_layout(e->m).total);
+    else
+      rc = setup_launch(e, e->packed ? pick_pfsp_kernel2<3>(mm) : pick_pfsp_kernel<3>(mm),
+                        bbk::pfsp_layout(e->m, e->T.P, 3, e->packed ? 2 : 1).total);
     if (rc)
       return rc;
     return build_graph(e);
@@ -659,6 +730,13 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
                     : mm == 20 ? (const void *)bbk::pfsp_expand_lb2<20>
                                : (const void *)bbk::pfsp_expand_lb2<0>;
     rc = setup_launch(e, k, bbk::lb2_layout(e->m, e->T.P).total, BB_LB2_THREADS);
+    if (rc)
+      return rc;
+    return build_graph(e);
+  }
+  if (e->packed == 2 && lb != 2)
+  {
+    rc = setup_launch(e, lb == 0 ? pick_pfsp_kernel3<0>(mm) : pick_pfsp_kernel3<1>(mm), bbk::tpp_layout(e->m).total);
     if (rc)
       return rc;
     return build_graph(e);
@@ -678,11 +756,22 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
   e->kind = KIND_NQ;
   e->N = N;
   e->G = G;
+  e->nq_gen = cfg ? (cfg->packed >= 2 || cfg->packed < 0 ? 3 : cfg->packed + 1) : 3; /* `packed` selects the generation */
+  if (e->nq_gen == 3)
+  {
+    int rc = alloc_common(e, cfg, 2, 0);
+    if (rc)
+      return rc;
+    rc = setup_launch(e, (const void *)bbk::nq_expand3, 0);
+    if (rc)
+      return rc;
+    return build_graph(e);
+  }
   const int tw = bbk::nq_tail_words(N);
   int rc = alloc_common(e, cfg, 1, tw);
   if (rc)
     return rc;
-  const bool gen2 = cfg ? (cfg->packed != 0) : true; /* `packed` selects the second-generation kernels */
+  const bool gen2 = e->nq_gen == 2;
   const void *k = gen2 ? (tw == 0   ? (const void *)bbk::nq_expand2<0>
                           : tw == 1 ? (const void *)bbk::nq_expand2<1>
                                     : (const void *)bbk::nq_expand2<2>)
@@ -871,6 +960,8 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
     if (e->kind == KIND_PFSP)
       k_seed_pfsp<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->T, at, e->T.mp,
                                                  e->pool.nplanes);
+    else if (e->nq_gen == 3)
+      k_seed_nq3<<<blocks, 128, 0, e->stream>>>((const uint8_t *)stage, count, e->pool, e->N, at);
     else
       k_seed_nq<<<blocks, 128, 0, e->stream>>>((const uint8_t *)stage, count, e->pool, e->N, at);
     k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, count, e->grid * (e->threads / 32));
@@ -931,6 +1022,8 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     const int blocks = (cnt + 127) / 128;
     if (e->kind == KIND_PFSP)
       k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
+    else if (e->nq_gen == 3)
+      k_export_nq3<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, from, cnt, at, e->N);
     else
       k_export_nq<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, from, cnt, at, e->N);
     at += cnt;

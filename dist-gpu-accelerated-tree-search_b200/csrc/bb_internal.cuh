@@ -97,6 +97,7 @@ struct bb_pfsp_dev
    * the unrolled machine loop reads it as a constant-bank operand */
   uint32_t tails2[BB_MAX_MACHINES];
   int best_known;
+  uint32_t one; /* 1 at run time: multiplier of the IMAD that does an add on the FMA pipe (bb_pfsp_tpp.cuh) */
 };
 
 #define BB_CUDA_TRY(call)                                         \

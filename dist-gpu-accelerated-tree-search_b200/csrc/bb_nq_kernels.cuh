@@ -328,6 +328,7 @@ nq_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
       for (int i0 = 0; i0 < nsurv; i0 += 32)
       {
         const int i = i0 + lane;
+        const unsigned amask = __ballot_sync(0xffffffffu, i < nsurv); /* lane 0 is always in it */
         if (i < nsurv)
         {
           int p = 0;
@@ -369,7 +370,7 @@ nq_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
               patch ^= dx << (8 * (dbyte & 3));
             w[wi] ^= patch;
           }
-          const unsigned at = __shfl_sync(__activemask(), pos, 0);
+          const unsigned at = __shfl_sync(amask, pos, 0);
           if (at + (unsigned)nsurv > (unsigned)cap)
             atomicExch(&ctrl->error, 1);
           else
@@ -379,6 +380,204 @@ nq_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 #pragma unroll
             for (int t = 0; t < TW; t++)
               dtail[slot * TW + t] = w[4 + t];
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  finish_iteration(ctrl, cnt6, src, base, cap);
+}
+
+/*
+ * Third-generation N-Queens kernel: the attack masks travel with the node.
+ *
+ * ncu on nq_expand2 (profiles/r01_ncu_full_v4_nq_17_4194304.txt) showed the ALU pipe 68 % busy and DRAM at 12.5 %:
+ * every parent rebuilt its diagonal masks from the board in an O(depth) loop, and every child looked for its row in
+ * the unplaced part of the permutation byte by byte. Here the record is 32 bytes (two planes):
+ *     plane 0          board[0..15]
+ *     plane 1  .x      board[16..19]
+ *              .y      rows already used (bit r) | depth << 24
+ *              .z      rows of column `depth` attacked along the rising diagonals  (b + (depth - i) == r)
+ *              .w      rows of column `depth` attacked along the falling diagonals (b - (depth - i) == r)
+ * so isSafe (nqueens_c.c:80-96) for ALL rows of the next column is  free = ~(used | up | down)  - three operations
+ * - and a child's masks are  used | bit, (up | bit) << 1, (down | bit) >> 1. The lane that owns a parent lists its
+ * safe rows (lane, row) in shared memory; pass 2 is dense, one lane per child: the row's position in the unplaced
+ * part of the permutation is found with a zero-byte test over the five board words (the child must be the
+ * reference's node: board[depth] <-> board[k] swapped, nqueens_c.c:107-111), and the two planes go out as coalesced
+ * 16-byte stores. -g repeats the safety test G times behind a register barrier. Counts and children are the
+ * reference's; depth-N children are counted, not stored.
+ */
+__device__ __forceinline__ uint32_t nq_has_byte(uint32_t w, uint32_t rrrr)
+{
+  const uint32_t x = w ^ rrrr;
+  return (x - 0x01010101u) & ~x & 0x80808080u; /* lowest flagged byte is an exact match */
+}
+
+__global__ void __launch_bounds__(BB_CTA_THREADS, 4)
+nq_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+{
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int cap = pool.capacity;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base, TS = ctrl->tile;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t full = (N >= 32) ? 0xffffffffu : ((1u << N) - 1u);
+
+  /* per warp: two tile buffers of [plane][32] uint4 (the next tile is copied asynchronously while this one is
+   * expanded) and the list of children (parent lane << 8 | row) */
+  __shared__ uint4 tile_all[BB_WARPS_PER_CTA][2][2 * 32];
+  __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS];
+  uint16_t *surv_s = surv_all[warp];
+
+  const uint4 *__restrict__ splanes = pool.planes[src];
+  uint4 *__restrict__ dplanes = pool.planes[dst];
+
+  unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
+
+  const int ntiles = (nbatch + TS - 1) / TS;
+  const int tstride = gridDim.x * BB_WARPS_PER_CTA;
+  auto fetch_tile = [&](int tile, uint4 *dstbuf) {
+    if (tile < ntiles)
+    {
+      const int first = tile * TS;
+      if (lane < min(TS, nbatch - first))
+      {
+        const size_t node = (size_t)base + first + lane;
+#pragma unroll
+        for (int q = 0; q < 2; q++)
+        {
+          const unsigned sa = (unsigned)__cvta_generic_to_shared(dstbuf + q * 32 + lane);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(splanes + (size_t)q * cap + node)
+                       : "memory");
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  int buf = 0;
+  fetch_tile(blockIdx.x * BB_WARPS_PER_CTA + warp, tile_all[warp][0]);
+  for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += tstride)
+  {
+    const uint4 *tile_s = tile_all[warp][buf];
+    fetch_tile(tile + tstride, tile_all[warp][buf ^ 1]);
+    buf ^= 1;
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __syncwarp();
+    const int first = tile * TS;
+    const int cnt = min(TS, nbatch - first);
+
+    /* ---- per parent: the safe rows of the next column ---- */
+    uint32_t fr = 0u;
+    int kids = 0, cands = 0;
+    bool leaf = false;
+    if (lane < cnt)
+    {
+      const uint4 q1 = tile_s[32 + lane];
+      const int depth = (int)(q1.y >> 24);
+      uint32_t used = q1.y & 0x00ffffffu;
+      leaf = (depth + 1 == N);
+      cands = N - depth;
+      for (int g = 0; g < G; g++)
+      {
+        asm volatile("" : "+r"(used)); /* keep the G repetitions as real work, as the reference's -g intends */
+        fr = ~(used | q1.z | q1.w) & full;
+      }
+      kids = __popc(fr);
+    }
+    const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
+    const int incl = warp_incl_scan(wkids, lane);
+    const int nsurv = __shfl_sync(0xffffffffu, incl, 31);
+    const int allkids = __reduce_add_sync(0xffffffffu, kids);
+    const int allsol = __reduce_add_sync(0xffffffffu, leaf ? kids : 0);
+    const int allcand = __reduce_add_sync(0xffffffffu, cands);
+    if (lane == 0)
+    {
+      cnt6[0] += allkids; /* exploredTree counts every safe placement, leaves included */
+      cnt6[1] += allsol;
+      cnt6[2] += cnt;
+      cnt6[3] += allcand;
+    }
+    if (!leaf)
+    {
+      int at = incl - wkids;
+      uint32_t f = fr;
+      while (f)
+      {
+        const int r = __ffs(f) - 1;
+        f &= f - 1u;
+        surv_s[at++] = (uint16_t)((lane << 8) | r);
+      }
+    }
+    __syncwarp();
+
+    /* ---- one reservation per tile, then every lane writes one child ---- */
+    if (nsurv)
+    {
+      unsigned pos = 0;
+      if (lane == 0)
+        pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
+      for (int i0 = 0; i0 < nsurv; i0 += 32)
+      {
+        const int i = i0 + lane;
+        const unsigned amask = __ballot_sync(0xffffffffu, i < nsurv); /* lane 0 is always in it */
+        if (i < nsurv)
+        {
+          const int e = surv_s[i];
+          const int p = e >> 8, r = e & 0xff;
+          const uint4 q0 = tile_s[p], q1 = tile_s[32 + p];
+          uint32_t w[5] = {q0.x, q0.y, q0.z, q0.w, q1.x};
+          const int depth = (int)(q1.y >> 24);
+          const uint32_t bit = 1u << r;
+          /* where row r sits in the unplaced part of the permutation: first byte equal to r (padding bytes beyond
+           * N are zero and come later) */
+          const uint32_t rrrr = (uint32_t)r * 0x01010101u;
+          int k = 0;
+          {
+            uint32_t z = nq_has_byte(w[4], rrrr);
+            k = 16;
+#pragma unroll
+            for (int wi = 3; wi >= 0; wi--)
+            {
+              const uint32_t zz = nq_has_byte(w[wi], rrrr);
+              if (zz)
+              {
+                z = zz;
+                k = 4 * wi;
+              }
+            }
+            k += (__ffs(z) - 1) >> 3;
+          }
+          /* swap board[depth] <-> board[k]: byte k takes the old board[depth], byte depth takes r */
+          uint32_t bd = 0;
+#pragma unroll
+          for (int wi = 0; wi < 5; wi++)
+            if (wi == (depth >> 2))
+              bd = (w[wi] >> (8 * (depth & 3))) & 0xffu;
+          const uint32_t x = bd ^ (uint32_t)r;
+#pragma unroll
+          for (int wi = 0; wi < 5; wi++)
+          {
+            uint32_t patch = 0;
+            if (wi == (depth >> 2))
+              patch ^= x << (8 * (depth & 3));
+            if (wi == (k >> 2))
+              patch ^= x << (8 * (k & 3));
+            w[wi] ^= patch;
+          }
+          const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
+          const uint32_t up2 = ((q1.z | bit) << 1) & full;
+          const uint32_t down2 = (q1.w | bit) >> 1;
+          const unsigned at = __shfl_sync(amask, pos, 0);
+          if (at + (unsigned)nsurv > (unsigned)cap)
+            atomicExch(&ctrl->error, 1);
+          else
+          {
+            const size_t slot = (size_t)at + i;
+            dplanes[slot] = make_uint4(w[0], w[1], w[2], w[3]);
+            dplanes[(size_t)cap + slot] = make_uint4(w[4], used2, up2, down2);
           }
         }
       }

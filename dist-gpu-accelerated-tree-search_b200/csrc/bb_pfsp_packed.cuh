@@ -255,6 +255,7 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         for (int i0 = 0; i0 < nsurv; i0 += 32)
         {
           const int i = i0 + lane;
+          const unsigned amask = __ballot_sync(0xffffffffu, i < nsurv); /* lane 0 is always in it */
           if (i < nsurv)
           {
             const int e = surv_s[i];
@@ -310,7 +311,7 @@ pfsp_expand2(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
 #pragma unroll
             for (int wi = 6 + MP; wi < NPL * 4; wi++)
               w[wi] = 0u;
-            const unsigned at = __shfl_sync(__activemask(), pos, 0);
+            const unsigned at = __shfl_sync(amask, pos, 0);
             if (at + (unsigned)nsurv > (unsigned)cap)
               atomicExch(&ctrl->error, 1);
             else

@@ -9,8 +9,7 @@
  *     stalls the kernels and copies of every other thread on that GPU;
  *   - a host that has already handed all free device memory to its own pool (a solver embedding this library
  *     next to other GPU consumers), where a late cudaMalloc simply fails;
- *   - code running where the CUDA runtime forbids allocation, e.g. between cudaStreamBeginCapture and
- *     cudaStreamEndCapture, or in a latency-critical section that must not take the driver's allocation lock.
+ *   - a latency-critical section that must not take the driver's allocation lock.
  * For them this file offers the same expand step as the engine (the kernel is bbk::pfsp_expand, unchanged) with
  * every byte of working memory taken from ONE file-scope __device__ array that is part of the library image:
  * the control block (counters, append cursor), the repacked instance tables and the two structure-of-arrays
@@ -87,14 +86,28 @@ __global__ void k_static_begin(unsigned char *scratch, const static_tables tb, i
 }
 
 /* caller's parents (reference Node layout, device memory) -> records of stack 0, deriving front/remain/mask */
-__global__ void k_static_seed(const Node *__restrict__ parents, int count, uint4 *__restrict__ planes0, int n, int m,
-                              int mp, int nplanes, const uint8_t *__restrict__ p8)
+__global__ void k_static_seed(unsigned char *scratch, const Node *__restrict__ parents, int count,
+                              uint4 *__restrict__ planes0, int n, int m, int mp, int nplanes,
+                              const uint8_t *__restrict__ p8)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
   const int16_t *nd = reinterpret_cast<const int16_t *>(parents + i);
   const int depth = nd[0];
+  /* the parents are in device memory, so they can only be checked here: a depth outside 0..n-1 or a job id outside
+   * 0..n-1 would make the expand kernel index its tables out of range. Such a batch is refused as a whole: the
+   * control block's error flag turns the expand launch into a no-op and the result words report it. */
+  bool bad = depth < 0 || depth >= n;
+  for (int j = 0; j < n; j++)
+    bad = bad || nd[2 + j] < 0 || nd[2 + j] >= n;
+  if (bad)
+  {
+    bb_ctrl *c = reinterpret_cast<bb_ctrl *>(scratch + OFF_CTRL);
+    c->n = 0; /* pfsp_expand returns at once when the planned batch is empty */
+    atomicExch(&c->error, 1);
+    return;
+  }
   uint32_t w[NPL_MAX * 4];
   for (int q = 0; q < NPL_MAX * 4; q++)
     w[q] = 0;
@@ -133,13 +146,14 @@ __global__ void k_static_export(const unsigned char *__restrict__ scratch, const
                                 Node *__restrict__ children, int max_children, unsigned long long *__restrict__ result)
 {
   const bb_ctrl *c = reinterpret_cast<const bb_ctrl *>(scratch + OFF_CTRL);
-  const int produced = c->size[1];
+  const int produced = c->error ? 0 : c->size[1];
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0)
   {
+    /* a refused batch (malformed parent, see k_static_seed) reports no children and all-ones in the counters */
     result[0] = (unsigned long long)produced;
-    result[1] = c->tree;
-    result[2] = c->sol;
+    result[1] = c->error ? ~0ull : c->tree;
+    result[2] = c->error ? ~0ull : c->sol;
     result[3] = (unsigned long long)(unsigned int)c->best;
   }
   if (i >= produced || i >= max_children)
@@ -281,7 +295,7 @@ extern "C" int bb_pfsp_expand_static(const bb_pfsp_instance *ins, int lb, int be
   k_static_begin<<<1, 256, 0, s>>>(scratch, tb, best, count, n, grid * BB_WARPS_PER_CTA);
   if (count > 0)
   {
-    k_static_seed<<<(count + 127) / 128, 128, 0, s>>>(parents_d, count, planes0, n, m, mp, nplanes, T.p8);
+    k_static_seed<<<(count + 127) / 128, 128, 0, s>>>(scratch, parents_d, count, planes0, n, m, mp, nplanes, T.p8);
     const void *kernel = lb == 0 ? static_kernel<0>(mm) : static_kernel<1>(mm);
     int prefilter = 0;
     void *args[] = {&ctrl, &pool, &T, &prefilter};

@@ -195,10 +195,12 @@ int main(int argc, char *argv[])
   }
   print_phase("Initial search on CPU completed", res.warm_tree, res.warm_sol, res.warm_s);
   print_phase("Search on Parallel GPU completed", res.tree, res.sol, res.search_s);
+  /* the reference prints the CUMULATIVE counters in all three blocks (pfsp_multigpu_cuda.c:122-125, 478-481, 505-508);
+   * there is no CPU drain step here, so this block repeats the totals with a zero phase time */
   print_phase("Final on CPU completed", res.tree, res.sol, 0.0);
   printf("\nExploration terminated.\n");
   print_results(res.best, res.tree, res.sol, res.elapsed_s);
-  append_csv(inst, lb, D, 0, ws, res.best, m, M, T, &res, per);
+  append_csv(inst, lb, D, C, ws, res.best, m, M, T, &res, per);
   bb_pfsp_instance_free(ins);
   return 0;
 }

@@ -294,8 +294,8 @@ int bb_measure_slot_step_peak(int device, double *slot_steps_per_s);
  * One bound -> prune -> branch step over a batch of parents (what bb_engine_push_nodes + bb_engine_run(1) +
  * bb_engine_export_nodes do) for callers that must not allocate device memory while they work: host threads
  * that share a GPU with other threads (cudaMalloc/cudaFree synchronise the device and would stall them all),
- * hosts that have already given every free byte of HBM to their own pool, and code inside a stream capture or a
- * latency-critical section where the runtime's allocator may not be entered. It calls no cudaMalloc, cudaFree or
+ * hosts that have already given every free byte of HBM to their own pool, and latency-critical sections that must
+ * not enter the driver's allocator. It calls no cudaMalloc, cudaFree or
  * other allocating routine: its whole working set - control block, instance tables, both node stacks - is one
  * file-scope __device__ array of about 4.6 MiB inside libbbgpu.so (present once on every GPU that loads the
  * library, until the process exits).
@@ -303,7 +303,11 @@ int bb_measure_slot_step_peak(int device, double *slot_steps_per_s);
  *   ins         host instance tables (bb_pfsp_instance_*); lb: 0 = LB1_d, 1 = LB1 (LB2 is not offered here)
  *   best        incumbent to prune against
  *   parents_d   DEVICE pointer, `count` nodes in the reference layout; count <= BB_STATIC_MAX_PARENTS, larger
- *               batches are refused with BB_ERR_ARG (split them)
+ *               batches are refused with BB_ERR_ARG (split them). Every parent must be an inner node of this
+ *               instance: 0 <= depth < nb_jobs and prmu[0..nb_jobs) a permutation of 0..nb_jobs-1. The nodes are in
+ *               device memory, so this is checked on the device: a batch holding a parent with a depth or a job id
+ *               out of range is refused as a whole - result_d[0] = 0 children and result_d[1] = result_d[2] =
+ *               all-ones
  *   children_d  DEVICE pointer, room for max_children nodes; survivors beyond max_children are dropped, so
  *               compare result_d[0] with max_children (count * nb_jobs always suffices)
  *   result_d    DEVICE pointer to 4 x unsigned long long: children produced, exploredTree increment,

@@ -181,3 +181,17 @@ def random_nq_nodes(rng, N, count, min_depth=0, max_depth=None):
         out[i, 0] = int(rng.integers(min_depth, max_depth + 1))
         out[i, 1:1 + N] = rng.permutation(N)
     return out
+
+
+def oracle_one_level(inst_handle, n, lb, parents, best):
+    """one batch through the oracle: evaluate_gpu's bounds[] (orc_evaluate_chunk) then generate_children
+    (PFSP_lib.h:51-95). Returns (children, tree increment, sol increment, incumbent, child bounds evaluated)."""
+    L = oracle()
+    parents = np.ascontiguousarray(parents, dtype=np.int16)
+    nb = int((n - parents[:, 0]).sum())
+    bounds = np.zeros(max(nb, 1), np.int32)
+    L.orc_evaluate_chunk(inst_handle, lb, parents, len(parents), best, bounds)
+    tree, sol, b = C.c_ulonglong(0), C.c_ulonglong(0), C.c_int(best)
+    kids = np.zeros((max(nb, 1), NODE_I16), np.int16)
+    k = L.orc_generate_children(parents, len(parents), n, bounds, C.byref(tree), C.byref(sol), C.byref(b), kids)
+    return kids[:k], tree.value, sol.value, b.value, nb

@@ -17,15 +17,7 @@ def node_set(a, width):
     return sorted(tuple(int(v) for v in r[:width]) for r in a)
 
 
-def oracle_one_level(inst_handle, n, lb, parents, best):
-    L = orc.oracle()
-    nb = int((n - parents[:, 0]).sum())
-    bounds = np.zeros(max(nb, 1), np.int32)
-    L.orc_evaluate_chunk(inst_handle, lb, parents, len(parents), best, bounds)
-    tree, sol, b = C.c_ulonglong(0), C.c_ulonglong(0), C.c_int(best)
-    kids = np.zeros((max(nb, 1), orc.NODE_I16), np.int16)
-    k = L.orc_generate_children(parents, len(parents), n, bounds, C.byref(tree), C.byref(sol), C.byref(b), kids)
-    return kids[:k], tree.value, sol.value, b.value, nb
+oracle_one_level = orc.oracle_one_level
 
 
 @pytest.mark.parametrize("inst", [1, 14, 21])
