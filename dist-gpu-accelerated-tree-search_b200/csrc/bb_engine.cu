@@ -759,10 +759,11 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
   e->nq_gen = cfg ? (cfg->packed >= 2 || cfg->packed < 0 ? 3 : cfg->packed + 1) : 3; /* `packed` selects the generation */
   if (e->nq_gen == 3)
   {
+    const bool c_nq4 = getenv("BB_NQ_PER_TILE_CURSOR") == nullptr; /* debugging aid: nq_expand3 reserves per tile */
     int rc = alloc_common(e, cfg, 2, 0);
     if (rc)
       return rc;
-    rc = setup_launch(e, (const void *)bbk::nq_expand3, 0);
+    rc = setup_launch(e, c_nq4 ? (const void *)bbk::nq_expand4 : (const void *)bbk::nq_expand3, 0);
     if (rc)
       return rc;
     return build_graph(e);

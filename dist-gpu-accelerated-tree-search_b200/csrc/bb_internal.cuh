@@ -25,6 +25,7 @@
 #define BB_INTERNAL_CUH
 
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #include "bb_gpu.h"
@@ -37,27 +38,35 @@
  * a CUDA graph with no host round trip (replaces popBackBulk/pushBackBulk + the index prep of the reference). */
 struct __align__(256) bb_ctrl
 {
-  /* iteration plan, written by the last CTA of the previous iteration (or by the host when seeding) */
+  /* ---- first 128-byte line: read-mostly during a launch ----
+   * iteration plan, written by the last CTA of the previous iteration (or by the host when seeding) */
   int size[2];         /* top of each stack: live nodes are [bot, size) */
   int bot[2];          /* bottom of each stack: nodes below were donated to another GPU (oldest nodes go first) */
-  int hold[2];         /* reserved (always 0): donations are copied out of the pool before the thief is told */
   int src;             /* stack this iteration pops from */
   int n;               /* parents in this iteration's batch (0 = nothing to do) */
   int base;            /* index of the first parent of the batch in stack src */
   int tile;            /* parents per warp tile for this iteration */
+  /* search state */
+  int best;            /* incumbent upper bound (atomicMin) */
+  int M;               /* max parents per iteration */
+  int capacity;        /* nodes per stack */
+  int maxkids;         /* most children one parent can have (jobs / queens): bounds the growth of one iteration */
+  int max_pool;        /* high-water mark of size[0]+size[1] */
+  /* the last donation (k_donate_plan): which stack, from which index, how many nodes */
+  int don_stack, don_from, don_count;
+  int pad0[16];
+  /* ---- second line: what every warp of a launch hammers with atomics. It is kept apart from `best` and the plan:
+   * loads of the first line used to queue behind the cursor atomics in the L2 (ncu: a third of the stall samples
+   * of the LB1_d kernel sat on the load of `best`). ---- */
   unsigned int tail;   /* append cursor of stack dst = 1 - src */
   unsigned int ticket; /* CTAs finished in this iteration */
   unsigned int next_tile; /* dynamic tile hand-out of this iteration (staged LB2 kernel) */
-  /* search state */
-  int best;            /* incumbent upper bound (atomicMin) */
   int error;           /* sticky: 1 = pool overflow */
-  int M;               /* max parents per iteration */
-  int capacity;        /* nodes per stack */
-  int max_pool;        /* high-water mark of size[0]+size[1] */
-  int maxkids;         /* most children one parent can have (jobs / queens): bounds the growth of one iteration */
   /* counters */
   unsigned long long tree, sol, parents, evals, lb2_evals, lb2_pairs, iterations;
 };
+static_assert(sizeof(bb_ctrl) == 256, "bb_ctrl is two 128-byte lines");
+static_assert(offsetof(bb_ctrl, tail) == 128, "the cursor starts the second line");
 
 struct bb_pool
 {

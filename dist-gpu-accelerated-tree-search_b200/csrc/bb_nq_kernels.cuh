@@ -588,5 +588,228 @@ nq_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
   finish_iteration(ctrl, cnt6, src, base, cap);
 }
 
+/*
+ * Fourth-generation N-Queens kernel: nq_expand3's record and per-child work, but ONE cursor reservation per CTA.
+ *
+ * ncu on nq_expand3 (profiles/r02_ncu_a_nq_17.txt): 64 % of the warp-stall samples sit on the return of the
+ * per-tile atomicAdd on the destination cursor. The work per node had shrunk so far that the 131 072 same-address
+ * atomics of a 4 M-parent launch - served at about one per nanosecond by the L2 - WERE the launch time. With the
+ * masks in the record the number of children of a parent is popcount(free): known after reading 16 bytes. So every
+ * CTA takes a contiguous slice of the batch and works in rounds of <= NQ4_ROUND parents:
+ *   phase 1  all threads: read plane 1 of the slice (coalesced), free mask and child count per parent -> shared
+ *            memory, per-tile totals, a scan over the tiles, ONE atomicAdd for the round;
+ *   phase 2  warp tiles as in nq_expand3 (planes prefetched with cp.async, children listed per lane, one lane per
+ *            child), every child written at round base + tile base + index. No atomics, no waiting.
+ * Plane 1 is read twice per parent, the second time from L2 (a launch's plane 1 is 64 MB at M = 4 M).
+ */
+#define NQ4_ROUND 4096
+
+__global__ void __launch_bounds__(BB_CTA_THREADS, 4)
+nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+{
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int cap = pool.capacity;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t full = (N >= 32) ? 0xffffffffu : ((1u << N) - 1u);
+
+  __shared__ uint32_t free_s[NQ4_ROUND];           /* safe rows of the next column, 0 for parents at depth N-1 */
+  __shared__ int tile_base[NQ4_ROUND / 32 + 1];    /* exclusive prefix of the tiles' child counts */
+  __shared__ unsigned round_base;
+  __shared__ uint4 tile_all[BB_WARPS_PER_CTA][2][2 * 32];
+  __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS];
+  uint16_t *surv_s = surv_all[warp];
+
+  const uint4 *__restrict__ splanes = pool.planes[src];
+  uint4 *__restrict__ dplanes = pool.planes[dst];
+
+  unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
+
+  /* this CTA's slice of the batch: a multiple of 32 parents so that tiles never straddle two CTAs */
+  const int per = (((nbatch + (int)gridDim.x - 1) / (int)gridDim.x) + 31) & ~31;
+  const long long lo_ll = (long long)blockIdx.x * per;
+  const int lo = lo_ll < nbatch ? (int)lo_ll : nbatch;
+  const int hi = min(nbatch, lo + per);
+
+  for (int r0 = lo; r0 < hi; r0 += NQ4_ROUND)
+  {
+    const int rcnt = min(NQ4_ROUND, hi - r0);
+    const int rtiles = (rcnt + 31) >> 5;
+    /* ---- phase 1: free masks and child counts of the round ---- */
+    for (int i = threadIdx.x; i < rtiles * 32; i += BB_CTA_THREADS)
+    {
+      uint32_t fr = 0u;
+      int kids = 0, cands = 0;
+      bool leaf = false;
+      if (i < rcnt)
+      {
+        const uint4 q1 = __ldg(splanes + (size_t)cap + base + r0 + i);
+        const int depth = (int)(q1.y >> 24);
+        uint32_t used = q1.y & 0x00ffffffu;
+        leaf = (depth + 1 == N);
+        cands = N - depth;
+        for (int g = 0; g < G; g++)
+        {
+          asm volatile("" : "+r"(used)); /* keep the G repetitions as real work, as the reference's -g intends */
+          fr = ~(used | q1.z | q1.w) & full;
+        }
+        kids = __popc(fr);
+      }
+      const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
+      free_s[i] = leaf ? 0u : fr;
+      const int tot = __reduce_add_sync(0xffffffffu, wkids);
+      const int allkids = __reduce_add_sync(0xffffffffu, kids);
+      const int allsol = __reduce_add_sync(0xffffffffu, leaf ? kids : 0);
+      const int allcand = __reduce_add_sync(0xffffffffu, cands);
+      if (lane == 0)
+      {
+        tile_base[i >> 5] = tot;
+        cnt6[0] += allkids; /* exploredTree counts every safe placement, leaves included */
+        cnt6[1] += allsol;
+        cnt6[3] += allcand;
+      }
+    }
+    if (threadIdx.x == 0)
+      cnt6[2] += rcnt;
+    __syncthreads();
+    if (warp == 0)
+    {
+      /* exclusive scan over <= 128 tile totals: 4 per lane */
+      int v[4], sum = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+      {
+        const int t = lane * 4 + k;
+        v[k] = t < rtiles ? tile_base[t] : 0;
+        sum += v[k];
+      }
+      const int incl = warp_incl_scan(sum, lane);
+      int run = incl - sum;
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+      {
+        const int t = lane * 4 + k;
+        if (t < rtiles)
+          tile_base[t] = run;
+        run += v[k];
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      if (lane == 0)
+      {
+        unsigned at = 0;
+        if (total)
+        {
+          at = atomicAdd(&ctrl->tail, (unsigned)total);
+          if (at + (unsigned)total > (unsigned)cap)
+          {
+            atomicExch(&ctrl->error, 1);
+            at = 0xffffffffu; /* nothing of this round is written */
+          }
+        }
+        round_base = at;
+      }
+    }
+    __syncthreads();
+    const unsigned rbase = round_base;
+
+    /* ---- phase 2: warp tiles, one lane per child, no atomics ---- */
+    auto fetch_tile = [&](int t, uint4 *dstbuf) {
+      if (t < rtiles)
+      {
+        const int first = t * 32;
+        if (lane < min(32, rcnt - first))
+        {
+          const size_t node = (size_t)base + r0 + first + lane;
+#pragma unroll
+          for (int q = 0; q < 2; q++)
+          {
+            const unsigned sa = (unsigned)__cvta_generic_to_shared(dstbuf + q * 32 + lane);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(splanes + (size_t)q * cap + node)
+                         : "memory");
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int buf = 0;
+    fetch_tile(warp, tile_all[warp][0]);
+    for (int t = warp; t < rtiles; t += BB_WARPS_PER_CTA)
+    {
+      const uint4 *tile_s = tile_all[warp][buf];
+      fetch_tile(t + BB_WARPS_PER_CTA, tile_all[warp][buf ^ 1]);
+      buf ^= 1;
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
+      uint32_t f = free_s[t * 32 + lane];
+      const int nk = __popc(f);
+      const int incl = warp_incl_scan(nk, lane);
+      const int nsurv = __shfl_sync(0xffffffffu, incl, 31);
+      int at = incl - nk;
+      while (f)
+      {
+        const int r = __ffs(f) - 1;
+        f &= f - 1u;
+        surv_s[at++] = (uint16_t)((lane << 8) | r);
+      }
+      __syncwarp();
+      if (rbase != 0xffffffffu)
+        for (int i = lane; i < nsurv; i += 32)
+        {
+          const int e = surv_s[i];
+          const int p = e >> 8, r = e & 0xff;
+          const uint4 q0 = tile_s[p], q1 = tile_s[32 + p];
+          uint32_t w[5] = {q0.x, q0.y, q0.z, q0.w, q1.x};
+          const int depth = (int)(q1.y >> 24);
+          const uint32_t bit = 1u << r;
+          /* where row r sits in the unplaced part of the permutation: first byte equal to r (padding bytes beyond
+           * N are zero and come later) */
+          const uint32_t rrrr = (uint32_t)r * 0x01010101u;
+          uint32_t z = nq_has_byte(w[4], rrrr);
+          int k = 16;
+#pragma unroll
+          for (int wi = 3; wi >= 0; wi--)
+          {
+            const uint32_t zz = nq_has_byte(w[wi], rrrr);
+            if (zz)
+            {
+              z = zz;
+              k = 4 * wi;
+            }
+          }
+          k += (__ffs(z) - 1) >> 3;
+          /* swap board[depth] <-> board[k] (nqueens_c.c:107-111): byte k takes the old board[depth], byte depth r */
+          uint32_t bd = 0;
+#pragma unroll
+          for (int wi = 0; wi < 5; wi++)
+            if (wi == (depth >> 2))
+              bd = (w[wi] >> (8 * (depth & 3))) & 0xffu;
+          const uint32_t x = bd ^ (uint32_t)r;
+#pragma unroll
+          for (int wi = 0; wi < 5; wi++)
+          {
+            uint32_t patch = 0;
+            if (wi == (depth >> 2))
+              patch ^= x << (8 * (depth & 3));
+            if (wi == (k >> 2))
+              patch ^= x << (8 * (k & 3));
+            w[wi] ^= patch;
+          }
+          const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
+          const uint32_t up2 = ((q1.z | bit) << 1) & full;
+          const uint32_t down2 = (q1.w | bit) >> 1;
+          const size_t slot = (size_t)rbase + tile_base[t] + i;
+          dplanes[slot] = make_uint4(w[0], w[1], w[2], w[3]);
+          dplanes[(size_t)cap + slot] = make_uint4(w[4], used2, up2, down2);
+        }
+      __syncwarp();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads(); /* free_s / tile_base are reused by the next round */
+  }
+  finish_iteration(ctrl, cnt6, src, base, cap);
+}
+
 } // namespace bbk
 #endif

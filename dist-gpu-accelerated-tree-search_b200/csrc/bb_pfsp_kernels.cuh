@@ -135,9 +135,9 @@ __host__ __device__ inline pfsp_smem_layout pfsp_layout(int m, int P, int lb, in
  * cannot fill a batch and the other one is larger. */
 __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
 {
-  /* a drained stack rewinds to index 0 unless a peer is still copying a donated chunk out of it */
+  /* a drained stack rewinds to index 0 (donations are copied out of the pool before the thief is told) */
   for (int s = 0; s < 2; s++)
-    if (c->size[s] == c->bot[s] && c->hold[s] == 0)
+    if (c->size[s] == c->bot[s])
       c->size[s] = c->bot[s] = 0;
   const int avail[2] = {c->size[0] - c->bot[0], c->size[1] - c->bot[1]};
   const int total = avail[0] + avail[1];

@@ -22,6 +22,14 @@
  *
  * Pass 2 (branch + compact) is dense as before - one lane per survivor, one cursor reservation per tile - but reads
  * the parent's whole record with 16-byte shared-memory loads and its job's time row, instead of one load per value.
+ *
+ * Nothing waits for the cursor. The atomicAdd that reserves a tile's slots comes back after 1-2 microseconds (every
+ * warp of the grid hits the same address; first capture of this kernel, profiles/r02_ncu_a_pfsp_*.txt: 12 % of the
+ * stall samples of the LB2 variant and 36 % of the LB1_d variant sat on its return, another 11 % / 33 % on the load of
+ * the incumbent, which shared the cursor's cache line). So a tile's pass 2 runs one tile LATE: the warp issues the
+ * reservation for tile t, bounds tile t+1, and only then writes tile t's children - three tile buffers rotate
+ * (pass 2 pending / being bounded / being prefetched with cp.async) and two survivor lists. The incumbent is loaded
+ * one tile ahead as well and lives in a different cache line than the cursor (bb_ctrl).
  * Results are bit-identical to the earlier kernels (same child set, same counters).
  */
 #ifndef BB_PFSP_TPP_CUH
@@ -48,10 +56,10 @@ __host__ __device__ inline tpp_smem_layout tpp_layout(int m)
   o += (pw * BB_MAX_JOBS * 4 + 15) & ~15;
   L.off_warp = o;
   int w = 0;
-  L.off_tile = w; /* 2 x [plane][32] uint4: the current tile and the one being prefetched */
-  w += 2 * pfsp_planes(m) * BB_TILE_MAX * 16;
-  L.off_surv = w; /* survivors of the tile: (parent lane << 8) | position in prmu */
-  w += BB_TILE_MAX * BB_MAX_JOBS * 2;
+  L.off_tile = w; /* 3 x [plane][32] uint4: pass 2 pending, being bounded, being prefetched */
+  w += 3 * pfsp_planes(m) * BB_TILE_MAX * 16;
+  L.off_surv = w; /* 2 x survivors of a tile: (parent lane << 8) | position in prmu */
+  w += 2 * BB_TILE_MAX * BB_MAX_JOBS * 2;
   L.warp_bytes = (w + 15) & ~15;
   L.total = o + L.warp_bytes * BB_WARPS_PER_CTA;
   return L;
@@ -83,7 +91,7 @@ __device__ __forceinline__ uint32_t add_fma(uint32_t a, uint32_t one, uint32_t b
 }
 
 template <int LB, int MM>
-__global__ void __launch_bounds__(BB_CTA_THREADS, (LB == 3 ? 2 : 3))
+__global__ void __launch_bounds__(BB_CTA_THREADS, ((LB == 3 || MM == 20 || MM == 0) ? 2 : 3))
 pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T, const int prefilter)
 {
   static_assert(LB == 0 || LB == 1 || LB == 3, "lane-per-parent kernel: LB1_d, LB1, LB2 through the subset table");
@@ -108,7 +116,6 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   uint32_t *prow = reinterpret_cast<uint32_t *>(smem + L.off_prow);
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
   uint4 *tile_buf = reinterpret_cast<uint4 *>(wbase + L.off_tile);
-  uint16_t *surv_s = reinterpret_cast<uint16_t *>(wbase + L.off_surv);
 
   for (int i = threadIdx.x; i < PW * BB_MAX_JOBS; i += BB_CTA_THREADS)
   {
@@ -148,17 +155,119 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  int buf = 0;
+  /* pass 2 of one tile: every lane writes one survivor at the reserved position */
+  auto write_children = [&](const uint4 *tile_s, const uint16_t *surv, int nsurv, unsigned pos) {
+    const unsigned char *tile_b = reinterpret_cast<const unsigned char *>(tile_s);
+    const unsigned at = __shfl_sync(0xffffffffu, pos, 0);
+    if (at + (unsigned)nsurv > (unsigned)cap)
+    {
+      if (lane == 0)
+        atomicExch(&ctrl->error, 1);
+      return;
+    }
+    for (int i = lane; i < nsurv; i += 32)
+    {
+      const int e = surv[i];
+      const int p = e >> 8, k = e & 0xff;
+      uint32_t W[NPL * 4];
+#pragma unroll
+      for (int q = 0; q < NPL; q++)
+      {
+        const uint4 v = tile_s[q * 32 + p];
+        W[4 * q] = v.x;
+        W[4 * q + 1] = v.y;
+        W[4 * q + 2] = v.z;
+        W[4 * q + 3] = v.w;
+      }
+      const int pdepth = (int)(W[5] & 0xffu);
+      const int job = tile_b[(k >> 4) * 512 + p * 16 + (k & 15)];
+      const int jobd = tile_b[(pdepth >> 4) * 512 + p * 16 + (pdepth & 15)];
+      uint32_t pw[PW];
+#pragma unroll
+      for (int q = 0; q < PW; q++)
+        pw[q] = prow[q * BB_MAX_JOBS + job];
+      /* prmu: swap positions depth and k (PFSP_lib.h:80-82) */
+      const uint32_t x = (uint32_t)(job ^ jobd);
+#pragma unroll
+      for (int wi = 0; wi < 5; wi++)
+      {
+        uint32_t patch = 0;
+        if (wi == (pdepth >> 2))
+          patch ^= x << (8 * (pdepth & 3));
+        if (wi == (k >> 2))
+          patch ^= x << (8 * (k & 3));
+        W[wi] ^= patch;
+      }
+      W[5] = (uint32_t)(pdepth + 1) | (((W[5] >> 8) | (1u << job)) << 8);
+      /* child front (completion times of the job after the parent's prefix) and remain (minus the job) */
+      uint32_t fo[MP / 2], ro[MP / 2];
+      {
+        int s = (int)(W[FW] & 0xffffu), tprev = 0;
+#pragma unroll
+        for (int i = 0; i < MP; i++)
+        {
+          int t = 0;
+          if (i < MU && (MM || i < m))
+          {
+            const uint32_t word = pw[i >> 2];
+            const int pj = (int)((i & 3) == 0   ? prmt_c<0x4440>(word, 0u)
+                                 : (i & 3) == 1 ? prmt_c<0x4441>(word, 0u)
+                                 : (i & 3) == 2 ? prmt_c<0x4442>(word, 0u)
+                                                : prmt_c<0x4443>(word, 0u));
+            t = s + pj;
+            if (i + 1 < MU)
+            {
+              const uint32_t fw = W[FW + (i + 1) / 2];
+              const int fn = (int)(((i + 1) & 1) ? (fw >> 16) : (fw & 0xffffu));
+              s = __viaddmax_s32(s, pj, fn);
+            }
+          }
+          if (i & 1)
+            fo[i / 2] = (uint32_t)tprev | ((uint32_t)t << 16);
+          tprev = t;
+        }
+#pragma unroll
+        for (int q = 0; q < MP / 2; q++)
+        {
+          const uint32_t word = pw[q >> 1];
+          const uint32_t pp = (q & 1) ? prmt_c<0x4342>(word, 0u) : prmt_c<0x4140>(word, 0u);
+          ro[q] = W[RW + q] - pp;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < MP / 2; q++)
+      {
+        W[FW + q] = fo[q];
+        W[RW + q] = ro[q];
+      }
+#pragma unroll
+      for (int wi = 6 + MP; wi < NPL * 4; wi++)
+        W[wi] = 0u;
+      const size_t slot = (size_t)at + i;
+#pragma unroll
+      for (int q = 0; q < NPL; q++)
+        dplanes[(size_t)q * cap + slot] = make_uint4(W[4 * q], W[4 * q + 1], W[4 * q + 2], W[4 * q + 3]);
+    }
+  };
+
+  uint16_t *surv_buf = reinterpret_cast<uint16_t *>(wbase + L.off_surv);
+  int buf = 0, sbuf = 0;
+  /* the tile whose children are still to be written (its cursor reservation is in flight) */
+  int pend_nsurv = 0, pend_buf = 0, pend_sbuf = 0;
+  unsigned pend_pos = 0;
+  int best_next = *reinterpret_cast<volatile int *>(&ctrl->best);
   fetch_tile(blockIdx.x * BB_WARPS_PER_CTA + warp, tile_buf);
   for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += tstride)
   {
     const uint4 *tile_s = tile_buf + buf * (NPL * 32);
     const unsigned char *tile_b = reinterpret_cast<const unsigned char *>(tile_s);
-    fetch_tile(tile + tstride, tile_buf + (buf ^ 1) * (NPL * 32));
-    buf ^= 1;
+    uint16_t *surv_s = surv_buf + sbuf * (BB_TILE_MAX * BB_MAX_JOBS);
+    const int nbuf = buf == 2 ? 0 : buf + 1;
+    fetch_tile(tile + tstride, tile_buf + nbuf * (NPL * 32)); /* the third buffer: neither current nor pending */
     asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
-    const int best = *reinterpret_cast<volatile int *>(&ctrl->best);
+    const int best = best_next;
+    best_next = *reinterpret_cast<volatile int *>(&ctrl->best); /* used by the next tile: its latency is hidden */
     const int first = tile * TS;
     const int cnt = min(TS, nbatch - first);
     const bool mine = lane < cnt;
@@ -312,112 +421,28 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     }
     __syncwarp();
 
-    /* ---- pass 2: one reservation on the destination cursor per tile, then every lane writes one survivor ---- */
-    if (nsurv)
+    /* ---- write the PREVIOUS tile's children (its reservation was issued a whole tile ago), then reserve this
+     * tile's slots: the value comes back while the next tile is bounded. (In this order the register holding the
+     * reservation is never copied while the atomic is still in flight.) ---- */
+    if (pend_nsurv)
+      write_children(tile_buf + pend_buf * (NPL * 32), surv_buf + pend_sbuf * (BB_TILE_MAX * BB_MAX_JOBS), pend_nsurv,
+                     pend_pos);
+    pend_pos = 0;
+    if (nsurv && lane == 0)
     {
-      unsigned pos = 0;
-      if (lane == 0)
-      {
-        pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
-        cnt6[0] += nsurv;
-      }
-      for (int i0 = 0; i0 < nsurv; i0 += 32)
-      {
-        const int i = i0 + lane;
-        const unsigned amask = __ballot_sync(0xffffffffu, i < nsurv); /* lane 0 is always in it */
-        if (i < nsurv)
-        {
-          const int e = surv_s[i];
-          const int p = e >> 8, k = e & 0xff;
-          uint32_t W[NPL * 4];
-#pragma unroll
-          for (int q = 0; q < NPL; q++)
-          {
-            const uint4 v = tile_s[q * 32 + p];
-            W[4 * q] = v.x;
-            W[4 * q + 1] = v.y;
-            W[4 * q + 2] = v.z;
-            W[4 * q + 3] = v.w;
-          }
-          const int pdepth = (int)(W[5] & 0xffu);
-          const int job = tile_b[(k >> 4) * 512 + p * 16 + (k & 15)];
-          const int jobd = tile_b[(pdepth >> 4) * 512 + p * 16 + (pdepth & 15)];
-          uint32_t pw[PW];
-#pragma unroll
-          for (int q = 0; q < PW; q++)
-            pw[q] = prow[q * BB_MAX_JOBS + job];
-          /* prmu: swap positions depth and k (PFSP_lib.h:80-82) */
-          const uint32_t x = (uint32_t)(job ^ jobd);
-#pragma unroll
-          for (int wi = 0; wi < 5; wi++)
-          {
-            uint32_t patch = 0;
-            if (wi == (pdepth >> 2))
-              patch ^= x << (8 * (pdepth & 3));
-            if (wi == (k >> 2))
-              patch ^= x << (8 * (k & 3));
-            W[wi] ^= patch;
-          }
-          W[5] = (uint32_t)(pdepth + 1) | (((W[5] >> 8) | (1u << job)) << 8);
-          /* child front (completion times of the job after the parent's prefix) and remain (minus the job) */
-          uint32_t fo[MP / 2], ro[MP / 2];
-          {
-            int s = (int)(W[FW] & 0xffffu), tprev = 0;
-#pragma unroll
-            for (int i = 0; i < MP; i++)
-            {
-              int t = 0;
-              if (i < MU && (MM || i < m))
-              {
-                const uint32_t word = pw[i >> 2];
-                const int pj = (int)((i & 3) == 0   ? prmt_c<0x4440>(word, 0u)
-                                     : (i & 3) == 1 ? prmt_c<0x4441>(word, 0u)
-                                     : (i & 3) == 2 ? prmt_c<0x4442>(word, 0u)
-                                                    : prmt_c<0x4443>(word, 0u));
-                t = s + pj;
-                if (i + 1 < MU)
-                {
-                  const uint32_t fw = W[FW + (i + 1) / 2];
-                  const int fn = (int)(((i + 1) & 1) ? (fw >> 16) : (fw & 0xffffu));
-                  s = __viaddmax_s32(s, pj, fn);
-                }
-              }
-              if (i & 1)
-                fo[i / 2] = (uint32_t)tprev | ((uint32_t)t << 16);
-              tprev = t;
-            }
-#pragma unroll
-            for (int q = 0; q < MP / 2; q++)
-            {
-              const uint32_t word = pw[q >> 1];
-              const uint32_t pp = (q & 1) ? prmt_c<0x4342>(word, 0u) : prmt_c<0x4140>(word, 0u);
-              ro[q] = W[RW + q] - pp;
-            }
-          }
-#pragma unroll
-          for (int q = 0; q < MP / 2; q++)
-          {
-            W[FW + q] = fo[q];
-            W[RW + q] = ro[q];
-          }
-#pragma unroll
-          for (int wi = 6 + MP; wi < NPL * 4; wi++)
-            W[wi] = 0u;
-          const unsigned at = __shfl_sync(amask, pos, 0);
-          if (at + (unsigned)nsurv > (unsigned)cap)
-            atomicExch(&ctrl->error, 1);
-          else
-          {
-            const size_t slot = (size_t)at + i;
-#pragma unroll
-            for (int q = 0; q < NPL; q++)
-              dplanes[(size_t)q * cap + slot] = make_uint4(W[4 * q], W[4 * q + 1], W[4 * q + 2], W[4 * q + 3]);
-          }
-        }
-      }
+      pend_pos = atomicAdd(&ctrl->tail, (unsigned)nsurv);
+      cnt6[0] += nsurv;
     }
+    pend_nsurv = nsurv;
+    pend_buf = buf;
+    pend_sbuf = sbuf;
+    buf = nbuf;
+    sbuf ^= 1;
     __syncwarp();
   }
+  if (pend_nsurv)
+    write_children(tile_buf + pend_buf * (NPL * 32), surv_buf + pend_sbuf * (BB_TILE_MAX * BB_MAX_JOBS), pend_nsurv,
+                   pend_pos);
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 
   finish_iteration(ctrl, cnt6, src, base, cap);
