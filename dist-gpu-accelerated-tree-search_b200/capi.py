@@ -102,8 +102,9 @@ EXPORTS = [
     "bb_pfsp_instance_taillard", "bb_pfsp_instance_from_ptimes", "bb_pfsp_instance_free", "bb_config_default",
     "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_engine_reset", "bb_engine_push_root",
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
-    "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist",
-    "bb_team_bytes", "bb_team_init", "bb_team_wait_ready", "bb_team_barrier", "bb_team_fail", "bb_team_worker",
+    "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist", "bb_pfsp_dist_open", "bb_nq_dist_open", "bb_dist_search",
+    "bb_dist_close",
+    "bb_team_bytes", "bb_team_init", "bb_team_reset", "bb_team_wait_ready", "bb_team_barrier", "bb_team_fail", "bb_team_worker",
     "bb_team_best", "bb_measure_slot_step_peak",
 ]
 
@@ -137,9 +138,17 @@ lib.bb_pfsp_search_dist.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, C
                                     C.POINTER(Config), C.POINTER(SearchResult), C.POINTER(Stats)]
 lib.bb_nq_search_dist.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(Config),
                                   C.POINTER(SearchResult), C.POINTER(Stats)]
+lib.bb_pfsp_dist_open.restype = _vp
+lib.bb_pfsp_dist_open.argtypes = [C.POINTER(PfspInstance), C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(Config)]
+lib.bb_nq_dist_open.restype = _vp
+lib.bb_nq_dist_open.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.POINTER(Config)]
+lib.bb_dist_search.argtypes = [_vp, C.c_int, C.c_int, C.POINTER(SearchResult), C.POINTER(Stats)]
+lib.bb_dist_close.restype = None
+lib.bb_dist_close.argtypes = [_vp]
 lib.bb_team_bytes.restype = C.c_size_t
 lib.bb_team_bytes.argtypes = [C.c_int]
 lib.bb_team_init.argtypes = [_vp, C.c_int]
+lib.bb_team_reset.argtypes = [_vp]
 lib.bb_team_wait_ready.argtypes = [_vp, C.c_int, C.c_double]
 lib.bb_team_barrier.argtypes = [_vp, C.c_double]
 lib.bb_team_fail.restype = None
@@ -296,6 +305,32 @@ def nq_search_dist(N, G, rank, world, shm_name, ws=1, **cfg):
     check(lib.bb_nq_search_dist(N, G, rank, world, shm_name.encode(), ws, C.byref(default_config(**cfg)),
                                 C.byref(res), C.byref(mine)), "bb_nq_search_dist")
     return res, mine
+
+
+class Dist:
+    """persistent multi-process team (bb_dist): open once, search many times; every rank makes the same calls"""
+
+    def __init__(self, rank, world, shm_name, instance=None, lb=None, N=None, G=1, **cfg):
+        self.instance = instance
+        c = default_config(**cfg)
+        if instance is not None:
+            self.h = lib.bb_pfsp_dist_open(instance.ptr, lb, rank, world, shm_name.encode(), C.byref(c))
+        else:
+            self.h = lib.bb_nq_dist_open(N, G, rank, world, shm_name.encode(), C.byref(c))
+        if not self.h:
+            raise BBError("bb_*_dist_open failed: " + last_error())
+
+    def search(self, best0=None, ws=1):
+        res, mine = SearchResult(), Stats()
+        if best0 is None:
+            best0 = self.instance.best_known if self.instance is not None else INT_MAX
+        check(lib.bb_dist_search(self.h, best0, ws, C.byref(res), C.byref(mine)), "bb_dist_search")
+        return res, mine
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib.bb_dist_close(self.h)
+            self.h = None
 
 
 def nq_search(N, G=1, D=1, ws=1, **cfg):

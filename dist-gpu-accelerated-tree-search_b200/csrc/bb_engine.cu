@@ -64,6 +64,8 @@ enum
   KIND_NQ = 2
 };
 
+#define BB_STAGE_SLOTS 2
+
 struct bb_engine
 {
   int kind;
@@ -74,8 +76,13 @@ struct bb_engine
   bb_pool pool;
   void *pool_mem[2];
   void *tail_mem[2];
-  void *stage_mem;        /* transfer buffer for donations (multi-GPU searches only) */
-  long long stage_nodes;
+  void *stage_mem;        /* transfer buffer for donations (multi-GPU searches only): BB_STAGE_SLOTS slots */
+  long long stage_nodes;  /* nodes per slot */
+  int slot_busy[BB_STAGE_SLOTS]; /* slot holds a donation its thief has not acknowledged yet */
+  int don_slot;           /* slot of the donation enqueued on the stream whose outcome is not fetched yet, or -1 */
+  volatile int *mailbox_h; /* pinned + mapped: (stack, count) of the last donation, written by k_donate_plan */
+  int *mailbox_d;
+  cudaEvent_t don_ev;
   /* PFSP */
   bb_pfsp_dev T;
   void *table_mem;
@@ -700,7 +707,10 @@ static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const 
   {
     /* build the subset table once per engine: 2^n rows of grow uint16 (part of the instance tables, like the
      * Johnson schedules the reference precomputes on the host) */
-    const int grow = ((e->m - 1) + 7) & ~7;
+    /* row length: what the kernel class loads ((MU - 1) entries rounded up to whole 16-byte pieces, MU = 20 for
+     * machine counts without a specialised kernel), so that a row read never leaves the table */
+    const int mu = bbk::pfsp_mm(e->m) ? bbk::pfsp_mm(e->m) : BB_MAX_MACHINES;
+    const int grow = ((mu - 1) + 7) & ~7;
     const size_t rows = (size_t)1 << e->n;
     rc = pool_alloc(e, &e->g16_mem, rows * grow * sizeof(uint16_t));
     if (rc)
@@ -861,7 +871,11 @@ extern "C" void bb_engine_destroy(bb_engine *e)
     pool_free(e, e->pool_mem[s]);
     pool_free(e, e->tail_mem[s]);
     if (s == 0 && e->stage_mem)
+    {
       cudaFree(e->stage_mem);
+      cudaFreeHost((void *)e->mailbox_h);
+      cudaEventDestroy(e->don_ev);
+    }
   }
   if (e->table_mem)
     cudaFree(e->table_mem);
@@ -904,6 +918,14 @@ extern "C" int bb_engine_reset(bb_engine *e, int best)
   if (e->kind == KIND_PFSP && e->staged)
     k_lb2_reset_order<<<1, 256, 0, e->stream>>>(e->T); /* a new search learns its pair order from scratch */
   BB_CUDA_TRY(cudaGetLastError());
+  if (e->stage_mem)
+  { /* a new search: no donation outstanding */
+    if (e->don_slot >= 0)
+      cudaEventSynchronize(e->don_ev);
+    e->don_slot = -1;
+    for (int s = 0; s < BB_STAGE_SLOTS; s++)
+      e->slot_busy[s] = 0;
+  }
   e->kernel_ms = 0;
   e->span_ms = 0;
   e->launches = 0;
@@ -1083,107 +1105,204 @@ extern "C" int bb_engine_get_stats(bb_engine *e, bb_stats *out)
  * bottom: shallow nodes, large sub-trees); the thief copies the planes straight out of the victim's HBM over
  * NVLink (peer access in one process, CUDA IPC between processes) and appends them to its own stack. */
 
-__global__ void k_donate(bb_ctrl *c, int stack, int count, int total_warps)
+/* Donation, device side. The victim's host thread never waits for its GPU: it ENQUEUES two kernels between two
+ * batches of iterations and goes on launching; the result arrives in a pinned mailbox.
+ *   k_donate_plan  decides on the state the pool really has at that point of the stream (not on the host's view,
+ *                  which is one batch old): the oldest half of the fuller stack, capped by the transfer-buffer slot;
+ *                  moves that stack's bottom up, re-plans the next iteration, publishes (stack, count);
+ *   k_donate_copy  copies the reserved nodes' planes into the slot (compact, plane-major). */
+__global__ void k_donate_plan(bb_ctrl *c, long long min_keep, long long max_count, int total_warps, volatile int *mailbox)
 {
-  if (threadIdx.x == 0 && blockIdx.x == 0)
+  if (threadIdx.x != 0 || blockIdx.x != 0)
+    return;
+  const long long a0 = c->size[0] - c->bot[0], a1 = c->size[1] - c->bot[1];
+  long long give = 0;
+  const int s = a0 >= a1 ? 0 : 1;
+  if (!c->error && a0 + a1 >= 2 * min_keep && a0 + a1 >= 2)
   {
-    c->bot[stack] += count;
+    give = (a0 + a1) / 2;
+    const long long as = s == 0 ? a0 : a1;
+    if (give > as)
+      give = as;
+    if (give > max_count)
+      give = max_count;
+  }
+  c->don_stack = s;
+  c->don_from = c->bot[s];
+  c->don_count = (int)give;
+  if (give > 0)
+  {
+    c->bot[s] += (int)give;
     bbk::plan_next(c, c->src, total_warps); /* the planned batch may have reached into the donated range */
+  }
+  mailbox[0] = s;
+  mailbox[1] = (int)give;
+}
+
+__global__ void __launch_bounds__(256) k_donate_copy(const bb_ctrl *__restrict__ c, const bb_pool pool,
+                                                    uint4 *__restrict__ slot)
+{
+  const int count = c->don_count, from = c->don_from, s = c->don_stack;
+  if (count <= 0)
+    return;
+  const uint4 *__restrict__ src = pool.planes[s];
+  const long long total = (long long)count * pool.nplanes;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+  {
+    const int q = (int)(i / count), k = (int)(i - (long long)q * count);
+    slot[i] = src[(size_t)q * pool.capacity + from + k];
+  }
+  if (pool.tail_words)
+  {
+    uint32_t *__restrict__ tw = reinterpret_cast<uint32_t *>(slot + total);
+    const uint32_t *__restrict__ st = pool.tailw[s] + (size_t)from * pool.tail_words;
+    const long long words = (long long)count * pool.tail_words;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (long long)gridDim.x * blockDim.x)
+      tw[i] = st[i];
   }
 }
 
-/* Transfer buffer of an engine that takes part in a multi-GPU search: a donation is copied out of the pool into
- * this buffer (plane-major, compact) and the thief reads the BUFFER, not the pool. Only this small allocation has
- * to be visible to the peers: mapping a whole multi-GB pool with cudaIpcOpenMemHandle costs ~50 ms per peer
- * (measured), mapping 128 MB about one. */
+/* thief side: append `count` records of a peer's transfer-buffer slot (peer or IPC-mapped pointer: plain loads over
+ * NVLink) to the top of our stack 0, wherever that is on the device at this point of the stream */
+__global__ void __launch_bounds__(256) k_pull_copy(bb_ctrl *__restrict__ c, const bb_pool pool,
+                                                  const uint4 *__restrict__ slot, int count)
+{
+  const int at = c->size[0];
+  if ((long long)at + count > pool.capacity)
+  {
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+      c->error = 1;
+    return;
+  }
+  uint4 *__restrict__ dst = pool.planes[0];
+  const long long total = (long long)count * pool.nplanes;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x)
+  {
+    const int q = (int)(i / count), k = (int)(i - (long long)q * count);
+    dst[(size_t)q * pool.capacity + at + k] = slot[i];
+  }
+  if (pool.tail_words)
+  {
+    const uint32_t *__restrict__ tw = reinterpret_cast<const uint32_t *>(slot + total);
+    uint32_t *__restrict__ dt = pool.tailw[0] + (size_t)at * pool.tail_words;
+    const long long words = (long long)count * pool.tail_words;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (long long)gridDim.x * blockDim.x)
+      dt[i] = tw[i];
+  }
+}
+
+__global__ void k_pull_commit(bb_ctrl *c, int count, int total_warps)
+{
+  if (threadIdx.x == 0 && blockIdx.x == 0 && !c->error)
+  {
+    c->size[0] += count;
+    bbk::plan_next(c, 0, total_warps);
+  }
+}
+
+/* Transfer buffer of an engine that takes part in a multi-GPU search: BB_STAGE_SLOTS slots, so that two donations
+ * can be outstanding. A donation is copied out of the pool into a slot (plane-major, compact) and the thief reads
+ * the SLOT, not the pool. Only this allocation has to be visible to the peers: mapping a whole multi-GB pool with
+ * cudaIpcOpenMemHandle costs ~50 ms per peer (measured), mapping the buffer a few. */
 int bb_engine_stage_alloc(bb_engine *e, size_t bytes)
 {
   ENGINE_SET_DEVICE(e);
+  if (e->stage_mem)
+    return BB_OK;
   const long long rec = (long long)e->pool.nplanes * 16 + (long long)e->pool.tail_words * 4;
-  long long nodes = (long long)(bytes / (size_t)rec);
+  long long nodes = (long long)(bytes / BB_STAGE_SLOTS / (size_t)rec);
   if (nodes > e->pool.capacity)
     nodes = e->pool.capacity;
+  nodes &= ~15ll; /* slots stay 256-byte aligned */
   if (nodes < 1024)
     return bb_fail(BB_ERR_ARG, "transfer buffer of %zu bytes is too small", bytes);
-  BB_CUDA_TRY(cudaMalloc(&e->stage_mem, (size_t)nodes * rec));
+  BB_CUDA_TRY(cudaMalloc(&e->stage_mem, (size_t)nodes * rec * BB_STAGE_SLOTS));
+  BB_CUDA_TRY(cudaHostAlloc((void **)&e->mailbox_h, 64, cudaHostAllocMapped));
+  BB_CUDA_TRY(cudaHostGetDevicePointer((void **)&e->mailbox_d, (void *)e->mailbox_h, 0));
+  BB_CUDA_TRY(cudaEventCreateWithFlags(&e->don_ev, cudaEventDisableTiming));
   e->stage_nodes = nodes;
+  e->don_slot = -1;
+  for (int s = 0; s < BB_STAGE_SLOTS; s++)
+    e->slot_busy[s] = 0;
   return BB_OK;
 }
 
 void *bb_engine_stage_ptr(bb_engine *e) { return e->stage_mem; }
+size_t bb_engine_stage_slot_bytes(bb_engine *e)
+{
+  return (size_t)e->stage_nodes * ((size_t)e->pool.nplanes * 16 + (size_t)e->pool.tail_words * 4);
+}
 
-/* victim side: reserve the oldest nodes of the fuller stack (they sit at the bottom: shallow nodes, large
- * sub-trees) and copy them into the transfer buffer; count = 0 when there is too little to share */
+/* victim side. First call: enqueue the donation behind the batch in flight and return *count = -1 ("pending; ask
+ * again"). Later calls: -1 until the GPU has got there, then the slot (in *stack) and the number of nodes it holds
+ * (0 = too little to share, or no free slot). The engine's stream is never synchronised. */
 int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int *stack, long long *start,
                      long long *count)
 {
   *count = 0;
+  *start = 0;
   if (!e->stage_mem)
     return bb_fail(BB_ERR_STATE, "bb_engine_donate: no transfer buffer");
   ENGINE_SET_DEVICE(e);
-  int rc = fetch_ctrl(e);
-  if (rc)
-    return rc;
-  const bb_ctrl *c = e->ctrl_h;
-  const long long a0 = c->size[0] - c->bot[0], a1 = c->size[1] - c->bot[1];
-  if (c->error || a0 + a1 < 2 * min_keep || a0 + a1 < 2)
+  if (e->don_slot < 0)
+  {
+    int slot = -1;
+    for (int s = 0; s < BB_STAGE_SLOTS; s++)
+      if (!e->slot_busy[s])
+        slot = s;
+    if (slot < 0)
+      return BB_OK; /* every slot still waits for its thief's acknowledgement */
+    if (max_count > e->stage_nodes)
+      max_count = e->stage_nodes;
+    uint4 *dst = (uint4 *)((char *)e->stage_mem + (size_t)slot * bb_engine_stage_slot_bytes(e));
+    k_donate_plan<<<1, 1, 0, e->stream>>>(e->ctrl, min_keep, max_count, e->grid * (e->threads / 32), e->mailbox_d);
+    k_donate_copy<<<128, 256, 0, e->stream>>>(e->ctrl, e->pool, dst);
+    BB_CUDA_TRY(cudaGetLastError());
+    BB_CUDA_TRY(cudaEventRecord(e->don_ev, e->stream));
+    e->don_slot = slot;
+    *count = -1;
     return BB_OK;
-  const int s = a0 >= a1 ? 0 : 1;
-  long long give = (a0 + a1) / 2;
-  if (give > (s == 0 ? a0 : a1))
-    give = s == 0 ? a0 : a1;
-  if (give > max_count)
-    give = max_count;
-  if (give > e->stage_nodes)
-    give = e->stage_nodes;
-  if (give <= 0)
+  }
+  const cudaError_t q = cudaEventQuery(e->don_ev);
+  if (q == cudaErrorNotReady)
+  {
+    *count = -1;
     return BB_OK;
-  const long long from = c->bot[s];
-  *stack = s;
-  *start = 0; /* offset inside the transfer buffer */
+  }
+  if (q != cudaSuccess)
+    return bb_fail_cuda(q, "donation", __FILE__, __LINE__);
+  const int give = e->mailbox_h[1];
+  *stack = e->don_slot;
   *count = give;
-  uint4 *stage = (uint4 *)e->stage_mem;
-  BB_CUDA_TRY(cudaMemcpy2DAsync(stage, (size_t)give * sizeof(uint4), e->pool.planes[s] + from,
-                                (size_t)e->pool.capacity * sizeof(uint4), (size_t)give * sizeof(uint4),
-                                e->pool.nplanes, cudaMemcpyDeviceToDevice, e->stream));
-  if (e->pool.tail_words)
-    BB_CUDA_TRY(cudaMemcpyAsync(stage + (size_t)give * e->pool.nplanes, e->pool.tailw[s] + from * e->pool.tail_words,
-                                (size_t)give * e->pool.tail_words * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
-                                e->stream));
-  k_donate<<<1, 1, 0, e->stream>>>(e->ctrl, s, (int)give, e->grid * (e->threads / 32));
-  BB_CUDA_TRY(cudaGetLastError());
-  return fetch_ctrl(e); /* synchronises: the buffer is complete before the thief is told about it */
-}
-
-int bb_engine_donate_done(bb_engine *e, int stack)
-{
-  (void)e;
-  (void)stack; /* the donation left the pool when it was copied out; the caller only frees the buffer for reuse */
+  if (give > 0)
+    e->slot_busy[e->don_slot] = 1;
+  e->don_slot = -1;
   return BB_OK;
 }
 
-/* thief side: append `count` records from a peer's transfer buffer (device pointer valid on this device) to the top
- * of our stack 0 */
-int bb_engine_pull(bb_engine *e, const void *peer_stage, long long count)
+int bb_engine_donate_done(bb_engine *e, int slot)
+{
+  if (slot >= 0 && slot < BB_STAGE_SLOTS)
+    e->slot_busy[slot] = 0; /* the thief has copied the slot out */
+  return BB_OK;
+}
+
+/* thief side: append `count` records from a peer's transfer-buffer slot (device pointer valid on this device) to
+ * the top of our stack 0; returns when the copy is complete, so that the caller may acknowledge */
+int bb_engine_pull(bb_engine *e, const void *peer_slot, long long count)
 {
   ENGINE_SET_DEVICE(e);
+  if (count <= 0)
+    return BB_OK;
+  k_pull_copy<<<128, 256, 0, e->stream>>>(e->ctrl, e->pool, (const uint4 *)peer_slot, (int)count);
+  k_pull_commit<<<1, 1, 0, e->stream>>>(e->ctrl, (int)count, e->grid * (e->threads / 32));
+  BB_CUDA_TRY(cudaGetLastError());
   int rc = fetch_ctrl(e);
   if (rc)
     return rc;
-  const long long at = e->ctrl_h->size[0];
-  if (at + count > e->pool.capacity)
+  if (e->ctrl_h->error)
     return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while taking over %lld nodes", e->pool.capacity, count);
-  const uint4 *stage = (const uint4 *)peer_stage;
-  BB_CUDA_TRY(cudaMemcpy2DAsync(e->pool.planes[0] + at, (size_t)e->pool.capacity * sizeof(uint4), stage,
-                                (size_t)count * sizeof(uint4), (size_t)count * sizeof(uint4), e->pool.nplanes,
-                                cudaMemcpyDeviceToDevice, e->stream));
-  if (e->pool.tail_words)
-    BB_CUDA_TRY(cudaMemcpyAsync(e->pool.tailw[0] + at * e->pool.tail_words, stage + (size_t)count * e->pool.nplanes,
-                                (size_t)count * e->pool.tail_words * sizeof(uint32_t), cudaMemcpyDeviceToDevice,
-                                e->stream));
-  k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, (int)count, e->grid * (e->threads / 32));
-  BB_CUDA_TRY(cudaGetLastError());
-  return fetch_ctrl(e);
+  return BB_OK;
 }
 
 /* zero the search counters but keep the pool (workers other than 0 after the common warm-up) */
@@ -1198,6 +1317,111 @@ int bb_engine_zero_counters(bb_engine *e)
   k_zero_counters<<<1, 1, 0, e->stream>>>(e->ctrl);
   BB_CUDA_TRY(cudaGetLastError());
   return fetch_ctrl(e);
+}
+
+/* Warm-up partition on the device (replaces roundRobin_distribution, Pool_atom.c:14-36): every worker has expanded
+ * the root to the same SET of nodes; it keeps the nodes whose placed prefix hashes to its id and drops the others, in
+ * place, stack by stack (one CTA: the warm-up pool is a few thousand nodes). A content hash needs no communication
+ * and does not depend on the order in which the device appended the nodes.
+ * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4), 2: N-Queens plane + tail words. */
+__global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, int mode, int nq_dbyte, int D, int me,
+                                                   int total_warps)
+{
+  __shared__ int warp_tot[32];
+  __shared__ int chunk_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int s = 0; s < 2; s++)
+  {
+    const int from = c->bot[s], to = c->size[s];
+    int out = from;
+    for (int c0 = from; c0 < to; c0 += blockDim.x)
+    {
+      const int i = c0 + threadIdx.x;
+      uint4 pl[7];
+      uint32_t tw[2] = {0u, 0u};
+      bool keep = false;
+      if (i < to)
+      {
+        for (int q = 0; q < pool.nplanes; q++)
+          pl[q] = pool.planes[s][(size_t)q * pool.capacity + i];
+        for (int t = 0; t < pool.tail_words; t++)
+          tw[t] = pool.tailw[s][(size_t)i * pool.tail_words + t];
+        uint32_t w[6] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w, 0u, 0u};
+        int depth;
+        if (mode == 0)
+        {
+          w[4] = pl[1].x;
+          depth = (int)(pl[1].y & 0xffu);
+        }
+        else if (mode == 1)
+        {
+          w[4] = pl[1].x;
+          depth = (int)(pl[1].y >> 24);
+        }
+        else
+        {
+          w[4] = tw[0];
+          w[5] = tw[1];
+          depth = (int)((w[nq_dbyte >> 2] >> (8 * (nq_dbyte & 3))) & 0xffu);
+        }
+        unsigned h = 2166136261u; /* FNV-1a over the placed prefix */
+        for (int b = 0; b < depth; b++)
+        {
+          h ^= (w[b >> 2] >> (8 * (b & 3))) & 0xffu;
+          h *= 16777619u;
+        }
+        h ^= h >> 15;
+        keep = (int)(h % (unsigned)D) == me;
+      }
+      /* block-wide exclusive scan of the keep flags */
+      const unsigned bal = __ballot_sync(0xffffffffu, keep);
+      if (lane == 0)
+        warp_tot[warp] = __popc(bal);
+      __syncthreads();
+      if (warp == 0)
+      {
+        const int v = lane < (int)(blockDim.x >> 5) ? warp_tot[lane] : 0;
+        const int incl = bbk::warp_incl_scan(v, lane);
+        warp_tot[lane] = incl - v;
+        if (lane == 31)
+          chunk_base = incl;
+      }
+      __syncthreads();
+      /* every record of this chunk is in registers: writing at out + rank (<= i) cannot clobber unread nodes */
+      if (keep)
+      {
+        const int at = out + warp_tot[warp] + __popc(bal & ((1u << lane) - 1u));
+        for (int q = 0; q < pool.nplanes; q++)
+          pool.planes[s][(size_t)q * pool.capacity + at] = pl[q];
+        for (int t = 0; t < pool.tail_words; t++)
+          pool.tailw[s][(size_t)at * pool.tail_words + t] = tw[t];
+      }
+      out += chunk_base;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0)
+      c->size[s] = out;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+    bbk::plan_next(c, c->src, total_warps);
+}
+
+/* keep this worker's share of the (common) warm-up pool; zero_counters: the warm-up counts are kept by the caller */
+int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters)
+{
+  ENGINE_SET_DEVICE(e);
+  int mode = 0, dbyte = 0;
+  if (e->kind == KIND_NQ)
+  {
+    mode = e->nq_gen == 3 ? 1 : 2;
+    dbyte = e->pool.tail_words ? 16 + (e->N - 16) : 15;
+  }
+  k_partition<<<1, 1024, 0, e->stream>>>(e->ctrl, e->pool, mode, dbyte, D, me, e->grid * (e->threads / 32));
+  if (zero_counters)
+    k_zero_counters<<<1, 1, 0, e->stream>>>(e->ctrl);
+  BB_CUDA_TRY(cudaGetLastError());
+  return BB_OK;
 }
 
 int bb_engine_kind_is_pfsp(const bb_engine *e) { return e->kind == KIND_PFSP; }

@@ -35,9 +35,11 @@
 int bb_engine_donate(bb_engine *e, long long min_keep, long long max_count, int *stack, long long *start,
                      long long *count);
 int bb_engine_donate_done(bb_engine *e, int stack);
-int bb_engine_pull(bb_engine *e, const void *peer_stage, long long count);
+int bb_engine_pull(bb_engine *e, const void *peer_slot, long long count);
 int bb_engine_stage_alloc(bb_engine *e, size_t bytes);
 void *bb_engine_stage_ptr(bb_engine *e);
+size_t bb_engine_stage_slot_bytes(bb_engine *e);
+int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters);
 int bb_engine_run_pipelined(bb_engine *e, long long iters, bb_stats *out);
 
 enum
@@ -78,7 +80,7 @@ struct device_span
   }
 };
 
-#define BB_STAGE_BYTES ((size_t)128 << 20) /* transfer buffer per GPU: the most one steal can move */
+#define BB_STAGE_BYTES ((size_t)256 << 20) /* transfer buffer per GPU: two slots, each the most one steal can move */
 
 struct ipc_slot
 {
@@ -136,12 +138,12 @@ int op_donate_done(void *self, int stack) { return bb_engine_donate_done(static_
 int op_pull(void *self, int victim, int stack, long long start, long long count)
 {
   gpu_worker *w = static_cast<gpu_worker *>(self);
-  (void)stack;
-  (void)start; /* the donation sits at the beginning of the victim's transfer buffer */
+  (void)start; /* the donation sits at the beginning of slot `stack` of the victim's transfer buffer */
   const int rc = ensure_peer_mapped(w, victim);
   if (rc)
     return rc;
-  return bb_engine_pull(w->e, w->peer_stage[victim], count);
+  const char *slot = static_cast<const char *>(w->peer_stage[victim]) + (size_t)stack * bb_engine_stage_slot_bytes(w->e);
+  return bb_engine_pull(w->e, slot, count);
 }
 
 int op_set_best(void *self, int best) { return bb_engine_set_best(static_cast<gpu_worker *>(self)->e, best); }
@@ -158,23 +160,13 @@ bb_team_ops gpu_ops(gpu_worker *w)
   return o;
 }
 
-/* worker of a node = FNV-1a of its placed prefix, mod D */
-inline unsigned prefix_hash(const unsigned char *bytes, int len)
-{
-  unsigned h = 2166136261u;
-  for (int i = 0; i < len; i++)
-  {
-    h ^= bytes[i];
-    h *= 16777619u;
-  }
-  return h ^ (h >> 15);
-}
-
-/* phase 1: common warm-up on this GPU, then keep this worker's share. Counters of the warm-up are returned in
- * base_* (the caller adds them for worker 0 only); the engine restarts with zero counters and the kept nodes. */
+/* phase 1: common warm-up on this GPU, then keep this worker's share (k_partition: hash of the placed prefix mod D,
+ * on the device, in place). Counters of the warm-up are returned in base_* (the caller adds them for worker 0 only);
+ * the engine continues with zero counters and the kept nodes. */
 int seed_partition(bb_engine *e, int kind, int D, int me, int m_keep, int best0, unsigned long long *base_tree,
                    unsigned long long *base_sol, int *best)
 {
+  (void)kind;
   bb_stats st;
   memset(&st, 0, sizeof(st));
   int rc = bb_engine_reset(e, best0);
@@ -197,30 +189,7 @@ int seed_partition(bb_engine *e, int kind, int D, int me, int m_keep, int best0,
   *best = st.best;
   if (st.pool_size == 0)
     return bb_engine_reset(e, st.best);
-  const size_t rec = kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
-  std::vector<unsigned char> all((size_t)st.pool_size * rec), keep;
-  const long long got = bb_engine_export_nodes(e, all.data(), st.pool_size);
-  if (got < 0)
-    return (int)got;
-  keep.reserve(all.size() / D + rec);
-  for (long long i = 0; i < got; i++)
-  {
-    const unsigned char *nd = all.data() + (size_t)i * rec;
-    unsigned h;
-    if (kind == KIND_PFSP)
-    {
-      const int16_t *p = reinterpret_cast<const int16_t *>(nd);
-      h = prefix_hash(reinterpret_cast<const unsigned char *>(p + 2), 2 * p[0]);
-    }
-    else
-      h = prefix_hash(nd + 1, nd[0]);
-    if ((int)(h % (unsigned)D) == me)
-      keep.insert(keep.end(), nd, nd + rec);
-  }
-  rc = bb_engine_reset(e, st.best);
-  if (!rc && !keep.empty())
-    rc = bb_engine_push_nodes(e, keep.data(), (int)(keep.size() / rec));
-  return rc;
+  return bb_engine_partition(e, D, me, 1);
 }
 
 bb_engine *create_engine(int kind, const bb_pfsp_instance *ins, int lb, int N, int G, const bb_config *cfg, int device)
@@ -377,17 +346,17 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       for (int j = 0; j < D; j++)
         w.peer_stage[j] = bb_engine_stage_ptr(W[j].e); /* peer access is enabled: direct pointers */
       int best = best0;
-      const double w0 = now_s();
+      /* the search is timed from the root: warm-up expansion and partition are inside the span */
+      const double s0 = now_s();
+      cudaSetDevice(i);
+      device_span span;
+      span.begin();
       int rc = seed_partition(w.e, kind, D, i, m_keep, best0, &o.base_tree, &o.base_sol, &best);
-      o.warm_s = now_s() - w0;
+      o.warm_s = now_s() - s0;
       if (rc)
         fail(rc);
-      if (bb_team_barrier(team, 120) == BB_OK && !o.rc)
+      if (!o.rc)
       {
-        const double s0 = now_s();
-        cudaSetDevice(i);
-        device_span span;
-        span.begin();
         bb_team_ops ops = gpu_ops(&w);
         rc = bb_team_worker(team, i, &ops, ws, m_keep, 5 * M, best, c.iters_per_launch, &o.tr);
         cudaSetDevice(i);
@@ -444,108 +413,186 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
   return rc;
 }
 
-/* ------------------------------------------------------------------ one process per GPU (torchrun): shm + CUDA IPC */
+/* ------------------------------------------------------------------ one process per GPU (torchrun): shm + CUDA IPC
+ * A persistent team: bb_*_dist_open creates the rank's engine, its transfer buffer and the mappings of every peer's
+ * buffer ONCE; bb_dist_search then runs whole searches on it (reset, root, common warm-up, device-side partition,
+ * stealing, termination) with nothing allocated, mapped or freed per search. bb_*_search_dist is open + search +
+ * close in one call. */
+
+struct bb_dist
+{
+  int kind, rank, world;
+  bb_config c;
+  int m_keep;
+  long long M;
+  bb_engine *e;
+  gpu_worker w;
+  void *mem;
+  size_t total, team_sz;
+  ipc_slot *I;
+  char shm_name[200];
+  double setup_s; /* engine creation (pool allocation, table upload, LB2 table build) */
+  double open_s;  /* the whole open call */
+  long long searches;
+};
 
 namespace
 {
 
-
-int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N, int G, int rank, int world,
-                const char *shm_name, int ws, const bb_config *cfg, bb_search_result *res, bb_stats *mine)
+void dist_free(bb_dist *d, bool team_alive)
 {
-  if (!res || !shm_name || world < 1 || world > 64 || rank < 0 || rank >= world)
-    return bb_fail(BB_ERR_ARG, "search_dist: bad arguments");
-  const double t0 = now_s();
-  bb_config c;
-  if (cfg)
-    c = *cfg;
-  else
-    bb_config_default(&c);
-  const int m_keep = c.m > 0 ? c.m : 25;
-  const long long M = c.M > 0 ? c.M : 50000;
-  const size_t team_sz = (bb_team_bytes(world) + 255) & ~(size_t)255;
-  const size_t total = team_sz + sizeof(ipc_slot) * (size_t)world;
-  const int fd = shm_open(shm_name, O_CREAT | O_RDWR, 0600);
-  if (fd < 0)
-    return bb_fail(BB_ERR_STATE, "shm_open(%s) failed", shm_name);
-  if (ftruncate(fd, (off_t)total) != 0)
+  if (!d)
+    return;
+  if (d->e)
+    cudaSetDevice(d->c.device);
+  for (int j = 0; j < d->world && j < 64; j++)
+    if (d->w.opened[j])
+      cudaIpcCloseMemHandle(d->w.peer_stage[j]);
+  if (team_alive && d->mem)
+    bb_team_barrier(d->mem, 60); /* every mapping of our buffer is closed before we free it */
+  if (d->e)
+    bb_engine_destroy(d->e);
+  if (d->mem)
+    munmap(d->mem, d->total);
+  if (d->rank == 0 && d->shm_name[0])
+    shm_unlink(d->shm_name);
+  free(d);
+}
+
+bb_dist *dist_open(int kind, const bb_pfsp_instance *ins, int lb, int N, int G, int rank, int world,
+                   const char *shm_name, const bb_config *cfg)
+{
+  if (!shm_name || world < 1 || world > 64 || rank < 0 || rank >= world || strlen(shm_name) >= 200)
   {
-    close(fd);
-    return bb_fail(BB_ERR_STATE, "ftruncate(%s) failed", shm_name);
+    bb_fail(BB_ERR_ARG, "dist_open: bad arguments");
+    return nullptr;
   }
-  void *mem = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  const double t0 = now_s();
+  bb_dist *d = static_cast<bb_dist *>(calloc(1, sizeof(bb_dist)));
+  d->kind = kind;
+  d->rank = rank;
+  d->world = world;
+  if (cfg)
+    d->c = *cfg;
+  else
+    bb_config_default(&d->c);
+  d->m_keep = d->c.m > 0 ? d->c.m : 25;
+  d->M = d->c.M > 0 ? d->c.M : 50000;
+  strcpy(d->shm_name, shm_name);
+  d->team_sz = (bb_team_bytes(world) + 255) & ~(size_t)255;
+  d->total = d->team_sz + sizeof(ipc_slot) * (size_t)world;
+  const int fd = shm_open(shm_name, O_CREAT | O_RDWR, 0600);
+  if (fd < 0 || ftruncate(fd, (off_t)d->total) != 0)
+  {
+    if (fd >= 0)
+      close(fd);
+    bb_fail(BB_ERR_STATE, "shm_open / ftruncate(%s) failed", shm_name);
+    free(d);
+    return nullptr;
+  }
+  d->mem = mmap(nullptr, d->total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
   close(fd);
-  if (mem == MAP_FAILED)
-    return bb_fail(BB_ERR_STATE, "mmap(%s) failed", shm_name);
-  ipc_slot *I = reinterpret_cast<ipc_slot *>(static_cast<char *>(mem) + team_sz);
-  int rc = rank == 0 ? bb_team_init(mem, world) : bb_team_wait_ready(mem, world, 120);
-  const bool trace = getenv("BB_TRACE_PHASES") != nullptr; /* per-rank phase times on stderr */
-  double tp[8];
-  tp[0] = now_s();
-  gpu_worker w;
-  memset(&w, 0, sizeof(w));
-  w.me = rank;
+  if (d->mem == MAP_FAILED)
+  {
+    bb_fail(BB_ERR_STATE, "mmap(%s) failed", shm_name);
+    free(d);
+    return nullptr;
+  }
+  d->I = reinterpret_cast<ipc_slot *>(static_cast<char *>(d->mem) + d->team_sz);
+  int rc = rank == 0 ? bb_team_init(d->mem, world) : bb_team_wait_ready(d->mem, world, 120);
+  d->w.me = rank;
+  if (!rc)
+  {
+    const double c0 = now_s();
+    d->e = create_engine(kind, ins, lb, N, G, &d->c, d->c.device);
+    d->setup_s = now_s() - c0;
+    if (!d->e)
+      rc = BB_ERR_CUDA;
+  }
+  if (!rc && world > 1)
+  {
+    rc = bb_engine_stage_alloc(d->e, BB_STAGE_BYTES);
+    if (!rc)
+    {
+      const cudaError_t err = cudaIpcGetMemHandle(&d->I[rank].stage, bb_engine_stage_ptr(d->e));
+      if (err != cudaSuccess)
+        rc = bb_fail_cuda(err, "cudaIpcGetMemHandle", __FILE__, __LINE__);
+      d->w.peer_stage[rank] = bb_engine_stage_ptr(d->e);
+    }
+  }
+  if (rc)
+    bb_team_fail(d->mem);
+  d->w.e = d->e;
+  d->w.ipc = d->I;
+  if (bb_team_barrier(d->mem, 180) != BB_OK && !rc)
+    rc = BB_ERR_STATE;
+  /* map every peer's transfer buffer now (a few ms each, once per team instead of inside the first steals) */
+  for (int j = 0; !rc && world > 1 && j < world; j++)
+    if (j != rank)
+      rc = ensure_peer_mapped(&d->w, j);
+  if (rc)
+    bb_team_fail(d->mem);
+  if (bb_team_barrier(d->mem, 180) != BB_OK && !rc)
+    rc = BB_ERR_STATE;
+  if (rc)
+  {
+    char msg[512];
+    strncpy(msg, bb_last_error(), sizeof(msg) - 1);
+    msg[sizeof(msg) - 1] = 0;
+    dist_free(d, false);
+    bb_fail(rc, "dist_open (rank %d): %s", rank, msg);
+    return nullptr;
+  }
+  d->open_s = now_s() - t0;
+  return d;
+}
+
+} // namespace
+
+extern "C" int bb_dist_search(bb_dist *d, int best0, int ws, bb_search_result *res, bb_stats *mine)
+{
+  if (!d || !res)
+    return bb_fail(BB_ERR_ARG, "bb_dist_search: bad arguments");
+  const double t0 = now_s();
+  const int rank = d->rank, world = d->world;
+  ipc_slot *I = d->I;
+  int rc = BB_OK;
+  /* every rank has left the previous search; rank 0 clears the team block; then everybody starts together */
+  if (bb_team_barrier(d->mem, 180) != BB_OK)
+    return BB_ERR_STATE;
+  if (rank == 0 && d->searches > 0)
+    bb_team_reset(d->mem);
+  if (bb_team_barrier(d->mem, 180) != BB_OK)
+    return BB_ERR_STATE;
+  d->searches++;
   bb_stats st;
   memset(&st, 0, sizeof(st));
   bb_team_result tr;
   memset(&tr, 0, sizeof(tr));
   unsigned long long base_tree = 0, base_sol = 0;
-  double search_s = 0;
-  auto fail = [&](int code) {
-    rc = code;
-    bb_team_fail(mem);
-  };
-  double setup_s = 0, warm_s = 0;
-  if (!rc)
-  {
-    const double c0 = now_s();
-    w.e = create_engine(kind, ins, lb, N, G, &c, c.device);
-    setup_s = now_s() - c0;
-    if (!w.e)
-      fail(BB_ERR_CUDA);
-  }
-  if (!rc && bb_engine_stage_alloc(w.e, BB_STAGE_BYTES) != BB_OK)
-    fail(BB_ERR_CUDA);
-  if (!rc)
-  {
-    const cudaError_t err = cudaIpcGetMemHandle(&I[rank].stage, bb_engine_stage_ptr(w.e));
-    if (err != cudaSuccess)
-      fail(bb_fail_cuda(err, "cudaIpcGetMemHandle", __FILE__, __LINE__));
-    w.peer_stage[rank] = bb_engine_stage_ptr(w.e);
-  }
-  tp[1] = now_s();
-  if (bb_team_barrier(mem, 180) != BB_OK && !rc)
-    rc = BB_ERR_STATE;
-  tp[2] = now_s();
-  w.ipc = I; /* peers' transfer buffers are mapped lazily, at the first steal (ensure_peer_mapped) */
   int best = best0;
-  tp[3] = now_s();
-  if (!rc)
+  /* the search is timed from the root: reset, root seeding, common warm-up and partition are inside the span */
+  const double s0 = now_s();
+  cudaSetDevice(d->c.device);
+  device_span span;
+  span.begin();
+  rc = seed_partition(d->e, d->kind, world, rank, d->m_keep, best0, &base_tree, &base_sol, &best);
+  const double warm_s = now_s() - s0;
+  double search_s = 0;
+  if (rc)
+    bb_team_fail(d->mem);
+  else
   {
-    const double w0 = now_s();
-    const int r2 = seed_partition(w.e, kind, world, rank, m_keep, best0, &base_tree, &base_sol, &best);
-    warm_s = now_s() - w0;
-    if (r2)
-      fail(r2);
-  }
-  if (bb_team_barrier(mem, 180) != BB_OK && !rc)
-    rc = BB_ERR_STATE;
-  if (!rc)
-  {
-    const double s0 = now_s();
-    cudaSetDevice(c.device);
-    device_span span;
-    span.begin();
-    bb_team_ops ops = gpu_ops(&w);
-    const int r2 = bb_team_worker(mem, rank, &ops, ws, m_keep, 5 * M, best, c.iters_per_launch, &tr);
-    cudaSetDevice(c.device);
+    d->w.kernel_ms_seen = 0;
+    bb_team_ops ops = gpu_ops(&d->w);
+    rc = bb_team_worker(d->mem, rank, &ops, ws, d->m_keep, 5 * d->M, best, d->c.iters_per_launch, &tr);
+    cudaSetDevice(d->c.device);
     search_s = span.end_s(now_s() - s0);
-    if (r2)
-      fail(r2);
+    if (rc)
+      bb_team_fail(d->mem);
     else
-      bb_engine_get_stats(w.e, &st);
+      bb_engine_get_stats(d->e, &st);
   }
-  tp[4] = now_s();
   I[rank].tree = st.tree + (rank == 0 ? base_tree : 0);
   I[rank].sol = st.sol + (rank == 0 ? base_sol : 0);
   I[rank].steals = tr.steals;
@@ -554,15 +601,15 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
   I[rank].kernel_ms = st.kernel_ms;
   I[rank].search_s = search_s;
   I[rank].warm_s = warm_s;
-  I[rank].setup_s = setup_s;
+  I[rank].setup_s = d->searches == 1 ? d->setup_s : 0.0;
   I[rank].warm_tree = rank == 0 ? base_tree : 0;
   I[rank].warm_sol = rank == 0 ? base_sol : 0;
   I[rank].best = tr.best;
+  I[rank].rc = rc;
   st.steals = tr.steals;
   st.steals_ok = tr.steals_ok;
   st.donated = tr.donated;
-  I[rank].rc = rc;
-  const int b1 = bb_team_barrier(mem, 180);
+  const int b1 = bb_team_barrier(d->mem, 180);
   memset(res, 0, sizeof(*res));
   res->best = INT_MAX;
   if (b1 == BB_OK && !rc)
@@ -590,41 +637,60 @@ int search_dist(int kind, const bb_pfsp_instance *ins, int lb, int best0, int N,
     }
   else if (!rc)
     rc = BB_ERR_STATE;
-  for (int j = 0; j < world; j++)
-    if (w.opened[j])
-      cudaIpcCloseMemHandle(w.peer_stage[j]);
-  tp[5] = now_s();
-  bb_team_barrier(mem, 60); /* every mapping of our pool is closed before we free it */
-  if (w.e)
-    bb_engine_destroy(w.e);
-  tp[6] = now_s();
-  if (trace)
-    fprintf(stderr, "[bb rank %d] create+handles %.1f ms, barrier %.1f, ipc open %.1f, warm-up..search end %.1f "
-                    "(search %.1f), reduce+close %.1f, destroy %.1f\n", rank, (tp[1] - tp[0]) * 1e3,
-            (tp[2] - tp[1]) * 1e3, (tp[3] - tp[2]) * 1e3, (tp[4] - tp[3]) * 1e3, search_s * 1e3, (tp[5] - tp[4]) * 1e3,
-            (tp[6] - tp[5]) * 1e3);
   if (mine)
     *mine = st;
-  munmap(mem, total);
-  if (rank == 0)
-    shm_unlink(shm_name);
   res->elapsed_s = now_s() - t0;
   return rc;
 }
 
-} // namespace
+extern "C" void bb_dist_close(bb_dist *d)
+{
+  if (d)
+    dist_free(d, true);
+}
+
+extern "C" bb_dist *bb_pfsp_dist_open(const bb_pfsp_instance *ins, int lb, int rank, int world, const char *shm_name,
+                                      const bb_config *cfg)
+{
+  if (!ins || lb < 0 || lb > 2)
+  {
+    bb_fail(BB_ERR_ARG, "bb_pfsp_dist_open: bad instance or lower bound");
+    return nullptr;
+  }
+  return dist_open(KIND_PFSP, ins, lb, 0, 0, rank, world, shm_name, cfg);
+}
+
+extern "C" bb_dist *bb_nq_dist_open(int N, int G, int rank, int world, const char *shm_name, const bb_config *cfg)
+{
+  return dist_open(KIND_NQ, nullptr, 0, N, G, rank, world, shm_name, cfg);
+}
+
+static int search_dist_once(bb_dist *d, int best0, int ws, bb_search_result *res, bb_stats *mine, double t0)
+{
+  if (!d)
+    return BB_ERR_STATE;
+  const int rc = bb_dist_search(d, best0, ws, res, mine);
+  bb_dist_close(d);
+  if (res)
+    res->elapsed_s = now_s() - t0;
+  return rc;
+}
 
 extern "C" int bb_pfsp_search_dist(const bb_pfsp_instance *ins, int lb, int best0, int rank, int world,
                                    const char *shm_name, int ws, const bb_config *cfg, bb_search_result *res,
                                    bb_stats *mine)
 {
-  if (!ins || lb < 0 || lb > 2)
-    return bb_fail(BB_ERR_ARG, "bb_pfsp_search_dist: bad instance or lower bound");
-  return search_dist(KIND_PFSP, ins, lb, best0, 0, 0, rank, world, shm_name, ws, cfg, res, mine);
+  if (!res)
+    return bb_fail(BB_ERR_ARG, "bb_pfsp_search_dist: bad arguments");
+  const double t0 = now_s();
+  return search_dist_once(bb_pfsp_dist_open(ins, lb, rank, world, shm_name, cfg), best0, ws, res, mine, t0);
 }
 
 extern "C" int bb_nq_search_dist(int N, int G, int rank, int world, const char *shm_name, int ws, const bb_config *cfg,
                                  bb_search_result *res, bb_stats *mine)
 {
-  return search_dist(KIND_NQ, nullptr, 0, INT_MAX, N, G, rank, world, shm_name, ws, cfg, res, mine);
+  if (!res)
+    return bb_fail(BB_ERR_ARG, "bb_nq_search_dist: bad arguments");
+  const double t0 = now_s();
+  return search_dist_once(bb_nq_dist_open(N, G, rank, world, shm_name, cfg), INT_MAX, ws, res, mine, t0);
 }

@@ -100,6 +100,7 @@ struct worker
   const bb_team_ops *ops;
   long long m_keep, max_steal;
   int outstanding[2], acks_seen[2];
+  bool donation_pending; /* ops->donate answered "pending" for the request in our slot */
   int best;
   unsigned rng;
 
@@ -119,7 +120,9 @@ struct worker
     return 0;
   }
 
-  /* answer the request waiting in our slot, if any: grant the oldest half of the pool or deny */
+  /* answer the request waiting in our slot, if any: grant the oldest half of the pool or deny. ops->donate may
+   * answer "pending" (count = -1: the GPU engine has only enqueued the donation behind the batch in flight and never
+   * waits for its device); the request then stays in our slot and is looked at again at the next poll. */
   int service_request(bool can_give)
   {
     const int req = ld(&mine().request);
@@ -128,17 +131,20 @@ struct worker
     team_slot &thief = S[req - 1];
     int stack = 0;
     long long start = 0, count = 0;
-    /* one donation at a time: the engine hands work over through a transfer buffer that stays busy until the
-     * thief acknowledges */
-    if (can_give && !ld(&H->finished) && outstanding[0] + outstanding[1] == 0)
+    /* a donation goes through one of the engine's two transfer-buffer slots, which stays busy until the thief
+     * acknowledges; the engine answers 0 when both are taken */
+    if (donation_pending || (can_give && !ld(&H->finished)))
     {
       int rc = ops->donate(ops->self, m_keep, max_steal, &stack, &start, &count);
       if (rc)
         return rc;
+      donation_pending = count < 0;
+      if (donation_pending)
+        return 0;
     }
     if (count > 0)
     {
-      outstanding[stack]++;
+      outstanding[stack & 1]++;
       mine().donated += (unsigned long long)count;
       thief.resp_victim = me;
       thief.resp_stack = stack;
@@ -270,6 +276,26 @@ extern "C" int bb_team_init(void *mem, int world)
   return BB_OK;
 }
 
+/* between two searches of a persistent team (every worker has left bb_team_worker and met in a barrier; one worker
+ * calls this, then a second barrier): forget the finished search, keep the barrier state */
+extern "C" int bb_team_reset(void *mem)
+{
+  team_hdr *H = static_cast<team_hdr *>(mem);
+  if (!H || __atomic_load_n(&H->magic, __ATOMIC_SEQ_CST) != TEAM_MAGIC)
+    return bb_fail(BB_ERR_ARG, "bb_team_reset: not a team block");
+  team_slot *S = slots_of(mem);
+  for (int i = 0; i < H->world; i++)
+  {
+    memset(&S[i], 0, sizeof(team_slot));
+    S[i].state = ST_BUSY;
+    S[i].best = INT_MAX;
+  }
+  st(&H->epoch, 0);
+  st(&H->finished, 0);
+  st(&H->failed, 0);
+  return BB_OK;
+}
+
 extern "C" int bb_team_wait_ready(void *mem, int world, double timeout_s)
 {
   team_hdr *H = static_cast<team_hdr *>(mem);
@@ -376,6 +402,11 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
     stll(&me_s.pool_size, 0);
     if ((rc = w.service_acks()) || (rc = w.service_request(false)))
       break;
+    if (w.donation_pending)
+    { /* the engine still owes the answer to a thief: do not hunt or go idle before it is given */
+      nap(10);
+      continue;
+    }
     if (w.outstanding[0] + w.outstanding[1] > 0)
     { /* a thief is still copying out of our memory: stay BUSY until it acknowledges */
       nap(20);
@@ -421,7 +452,8 @@ extern "C" int bb_team_worker(void *mem, int me, const bb_team_ops *ops, int ws,
   {
     w.service_request(false);
     w.service_acks();
-    if (w.outstanding[0] + w.outstanding[1] == 0 || ld(&H->failed) || now_ms() - t_exit > 30e3)
+    if ((w.outstanding[0] + w.outstanding[1] == 0 && !w.donation_pending) || ld(&H->failed) ||
+        now_ms() - t_exit > 30e3)
       break;
     nap(20);
   }

@@ -243,12 +243,25 @@ int bb_nq_search(int N, int G, int D, int ws, const bb_config *cfg, bb_search_re
 /* The same searches with one PROCESS per GPU (rank = 0..world-1 on one node, e.g. under torchrun): every rank calls
  * with the same arguments and its own cfg->device; ranks meet in the POSIX shared-memory object `shm_name`
  * (created by whoever arrives first, unlinked by rank 0 at the end; use a fresh name per call), exchange CUDA IPC
- * handles of their pools through it and steal from each other's HBM over NVLink. Every rank returns the global
+ * handles of their transfer buffers through it and steal from each other's HBM over NVLink. Every rank returns the global
  * totals in `res`; `mine` (may be NULL) gets the caller's own engine statistics. */
 int bb_pfsp_search_dist(const bb_pfsp_instance *ins, int lb, int best0, int rank, int world, const char *shm_name,
                         int ws, const bb_config *cfg, bb_search_result *res, bb_stats *mine);
 int bb_nq_search_dist(int N, int G, int rank, int world, const char *shm_name, int ws, const bb_config *cfg,
                       bb_search_result *res, bb_stats *mine);
+
+/* The same with a PERSISTENT team: open once per (instance, bound) - engine, pool, tables, transfer buffer and the
+ * CUDA IPC mappings of every peer's buffer are created here - then run any number of searches; nothing is allocated,
+ * mapped or freed per search. Every rank calls each function with the same arguments (collective calls). A search is
+ * timed from the root: res->search_s is the max over ranks of the span from just before the root is seeded (reset,
+ * root, common warm-up, device-side partition) to the detection of global termination; res->elapsed_s is the wall
+ * time of the bb_dist_search call on the calling rank. world = 1 is allowed (no stealing). */
+typedef struct bb_dist bb_dist;
+bb_dist *bb_pfsp_dist_open(const bb_pfsp_instance *ins, int lb, int rank, int world, const char *shm_name,
+                           const bb_config *cfg);
+bb_dist *bb_nq_dist_open(int N, int G, int rank, int world, const char *shm_name, const bb_config *cfg);
+int bb_dist_search(bb_dist *d, int best0, int ws, bb_search_result *res, bb_stats *mine);
+void bb_dist_close(bb_dist *d);
 
 /* ----- the team protocol underneath (host code only; replaces the steal loop pfsp_multigpu_cuda.c:343-404, the
  * allIdle termination common/util.c:19-38 and checkBest pfsp_multigpu_cuda.c:30-50). `mem` is a zero-filled block
@@ -259,7 +272,10 @@ typedef struct bb_team_ops
   void *self;
   /* run at most max_iters pool iterations; report nodes left, the incumbent and device time spent */
   int (*run)(void *self, long long max_iters, long long *pool_size, int *best, double *busy_ms);
-  /* reserve the oldest nodes of one stack for a thief: count = 0 when fewer than 2*min_keep nodes are left */
+  /* reserve the oldest nodes for a thief: count = 0 when fewer than 2*min_keep nodes are left (or no transfer slot is
+   * free), count = -1 when the answer is not known yet - the protocol then calls again at its next poll (the GPU
+   * engine only enqueues the donation on its stream and never waits for the device). `stack` names the stack / the
+   * transfer-buffer slot (0 or 1) the nodes sit in until donate_done. */
   int (*donate)(void *self, long long min_keep, long long max_count, int *stack, long long *start, long long *count);
   int (*donate_done)(void *self, int stack); /* the thief has copied the range out */
   /* thief side: copy [start, start+count) of `stack` out of worker `victim`'s memory into the own pool */
@@ -276,6 +292,7 @@ typedef struct bb_team_result
 
 size_t bb_team_bytes(int world);
 int bb_team_init(void *mem, int world);                          /* by one worker, before the others use mem */
+int bb_team_reset(void *mem);                                    /* by one worker, between two searches of the team */
 int bb_team_wait_ready(void *mem, int world, double timeout_s);  /* by the others */
 int bb_team_barrier(void *mem, double timeout_s);
 void bb_team_fail(void *mem);
