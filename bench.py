@@ -208,36 +208,73 @@ def kernel_key(w):
     return {0: "pfsp_expand_lb1d", 1: "pfsp_expand_lb1", 2: "pfsp_expand_lb2"}[w[2]]
 
 
-def roofline_objects(bb, w, rec_alg, rec_pool, parents, nodes, kernel_ms, iters, lb2_pairs, device, pairloop=False):
-    """HBM roofline of the expand kernel (algorithmic bytes: every explored node is written once as a survivor and
-    read once as a parent); for LB2 additionally the integer-pipe roofline in LB2 slot steps."""
+def alg_record_bytes(w, ins):
+    """record size SURVEY 8(d) sanctions: PFSP n bytes prmu + depth (+ pad) + the declared front cache uint16[m];
+    N-Queens N + depth. (The pool's own record also caches remain[] / the attack masks; that is reported beside it.)"""
+    if w[0] == "pfsp":
+        return ins.n + 2 + 2 * ins.m
+    return w[1] + 1
+
+
+def roofline_objects(bb, w, ins, rec_pool, parents, nodes, evals, lb2_evals, kernel_ms, iters, lb2_pairs, device,
+                     pairloop=False):
+    """HBM roofline of the expand kernel on SURVEY 8(d)'s algorithmic bytes: every explored node is written once as
+    a survivor and read once as a parent -> frac = (parents + nodes) x record / kernel time / measured copy peak.
+    For LB2 additionally the integer-pipe roofline: useful add/max operations by the authors' own model
+    (PFSP_gpu_lib.cu:244-254) against the measured VIADDMNMX rate."""
     peak, peak_src = measured_peaks()
+    rec_alg = alg_record_bytes(w, ins)
     alg_bytes = (parents + nodes) * rec_alg
     achieved = alg_bytes / (kernel_ms / 1e3) / 1e9
+    pool_bytes = (parents + nodes) * rec_pool
     tr = ncu_traffic(kernel_key(w))
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": tr["dram_bytes_per_launch"] if tr else None,
             "traffic_note": tr["note"] if tr else None, "peak_source": peak_src,
-            "kernel": {"nq_expand": "bbk::nq_expand", "pfsp_expand_lb2": "bbk::pfsp_expand_lb2"}.get(
-                kernel_key(w), "bbk::pfsp_expand"),
+            "kernel": {"nq_expand": "bbk::nq_expand4", "pfsp_expand_lb2": "bbk::pfsp_expand3<3,m>"}.get(
+                kernel_key(w), "bbk::pfsp_expand3<lb,m>"),
             "algorithmic_bytes_per_node": 2 * rec_alg, "record_bytes_in_pool": rec_pool,
-            "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1)}
+            "frac_pool_record": pool_bytes / (kernel_ms / 1e3) / 1e9 / peak,
+            "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1),
+            "ncu_limiter": tr.get("limiter") if tr else None}
     extra = {}
-    if w[0] == "pfsp" and w[2] == 2 and not pairloop:
-        roof["note"] = ("LB2 is evaluated through the per-instance subset table (2^n x (m-1) uint16, L2-resident): one "
-                        "48-byte row read per candidate child on top of the node records")
-    if w[0] == "pfsp" and w[2] == 2 and pairloop:
+    if w[0] == "pfsp" and w[2] == 2:
         pk = C.c_double(0)
         bb.check(bb.lib.bb_measure_slot_step_peak(device, C.byref(pk)), "bb_measure_slot_step_peak")
-        steps = lb2_pairs * 20  # each evaluated (child, pair) walks the 20 Johnson slots: one bit test + one add-max
-        ach = steps / (kernel_ms / 1e3)
-        roof["note"] = ("the LB2 pair loop is bound by the integer ALU pipe, not HBM (ncu: ALU pipe ~69 % busy, DRAM "
-                        "< 2 %); the binding roofline is roofline_int below")
-        extra["roofline_int"] = {"bound": "int_alu", "achieved": ach / 1e9, "peak": pk.value / 1e9,
-                                 "unit": "G slot-steps/s", "frac": ach / pk.value,
-                                 "peak_source": "measured in this run (bb_measure_slot_step_peak: LOP3 test + "
-                                                "predicated VIADDMNMX only, all SMs)",
-                                 "slot_steps_per_pair": 20}
+        if pairloop:
+            steps = lb2_pairs * 20  # each evaluated (child, pair) walks the 20 Johnson slots: bit test + add-max
+            ach = steps / (kernel_ms / 1e3)
+            roof["note"] = ("the LB2 pair loop is bound by the integer ALU pipe, not HBM; the binding roofline is "
+                            "roofline_int below")
+            extra["roofline_int"] = {"bound": "int_alu", "achieved": ach / 1e9, "peak": pk.value / 1e9,
+                                     "unit": "G slot-steps/s", "frac": ach / pk.value,
+                                     "peak_source": "measured in this run (bb_measure_slot_step_peak: LOP3 test + "
+                                                    "predicated VIADDMNMX only, all SMs)",
+                                     "slot_steps_per_pair": 20}
+        else:
+            # the authors' op model for one LB2 child bound: lim*(1+2(m-1)) + P*(4u+4), lim = scheduled jobs of the
+            # child, u = n - lim (PFSP_gpu_lib.cu:244-254); summed with the mean lim of the children bounded in this
+            # run (children per parent = n - depth) and ALL P pairs (the table covers every pair; the reference's
+            # early exit visits fewer, so this is an upper bound of its useful operations)
+            n, m, P = ins.n, ins.m, ins.P
+            lim = n - evals / max(parents, 1) + 1
+            ops_child = lim * (1 + 2 * (m - 1)) + P * (4 * (n - lim) + 4)
+            ops = evals * ops_child
+            ach = ops / (kernel_ms / 1e3)
+            int_peak = 2.0 * pk.value  # a slot step is two ALU-pipe instructions per lane (test + add-max)
+            roof["note"] = ("LB2 is evaluated through the per-instance subset table (2^n x (m-1) uint16, L2-resident): "
+                            "one 48-byte row read per child that passes the exact LB1_d prefilter, on top of the node "
+                            "records; ncu shows the kernel limited by the integer ALU pipe and L2 latency, not HBM")
+            extra["roofline_int"] = {"bound": "int_alu", "achieved": ach / 1e12, "peak": int_peak / 1e12,
+                                     "unit": "T model-ops/s", "frac": ach / int_peak,
+                                     "model": "authors' flop_lb2 (PFSP_gpu_lib.cu:244-254) with all P pairs per child "
+                                              "bound, mean lim of this run",
+                                     "model_ops_per_child_bound": ops_child, "child_bounds": evals,
+                                     "children_through_the_table": lb2_evals,
+                                     "peak_source": "measured in this run: 2 x bb_measure_slot_step_peak (ALU-pipe "
+                                                    "lane-instructions per second, all SMs)",
+                                     "note": "the table replaces the pair loops: the model counts the operations the "
+                                             "reference would spend on the same child bounds, so frac can exceed 1"}
     return roof, extra
 
 
@@ -246,18 +283,26 @@ def lb2kw(args):
     return dict(lb2_table=0) if args.lb2_pairloop else {}
 
 
+def shm_tag():
+    return f"/bbgpu_{os.getpid()}_{int(time.time() * 1e3) & 0xffffff}"
+
+
+def open_dist(bb, w, ins, rank, world, name, local_rank, args):
+    if w[0] == "pfsp":
+        return bb.Dist(rank, world, name, instance=ins, lb=w[2], device=local_rank, M=args.M, **lb2kw(args))
+    return bb.Dist(rank, world, name, N=w[1], G=1, device=local_rank, M=args.M)
+
+
 def run_single(args, w, bb, torch, local_rank):
     K, W = args.steps, max(args.warmup, 0)
     if w[0] == "pfsp":
         ins = bb.Instance(inst=w[1])
         eng = bb.Engine.pfsp(ins, w[2], device=local_rank, M=args.M, **lb2kw(args))
         best0 = ins.best_known
-        rec_alg = ins.n + 2 + 4 * ins.m  # prmu + depth (+pad) + cached front/remain uint16[m] each
     else:
         ins = None
         eng = bb.Engine.nqueens(w[1], 1, device=local_rank, M=args.M)
         best0 = bb.INT_MAX
-        rec_alg = w[1] + 1
 
     def one_step():
         eng.reset(best0)
@@ -290,22 +335,31 @@ def run_single(args, w, bb, torch, local_rank):
     if exp is not None and st.tree != exp:
         raise SystemExit(f"PARITY FAILURE: explored tree {st.tree} != reference {exp}")
     value = nodes / (span_ms / 1e3)
+    eng.close()
 
-    # e2e: the one-shot C-ABI call with host tables (creation + upload + search + teardown), wall clock
+    # e2e: the search call a user of the library makes on a context that is opened once per instance
+    # (bb_*_dist_open, world = 1): reset, root node from HOST memory (H2D), the search, control-block polls and the
+    # result (D2H) - wall clock around bb_dist_search. The one-shot call (open + search + close: engine creation,
+    # pool allocation, table upload, LB2 table build, teardown) is timed beside it.
+    d = open_dist(bb, w, ins, 0, 1, shm_tag(), local_rank, args)
+    d.search()
     e2e_t, e2e_nodes, e2e_h2d, e2e_d2h = 0.0, 0, 0, 0
-    for _ in range(max(1, min(K, 2))):
+    for _ in range(K):
         t = time.perf_counter()
-        if w[0] == "pfsp":
-            res, per = bb.pfsp_search(ins, w[2], device=local_rank, M=args.M, **lb2kw(args))
-        else:
-            res, per = bb.nq_search(w[1], 1, device=local_rank, M=args.M)
+        res, mine = d.search()
         e2e_t += time.perf_counter() - t
         e2e_nodes += res.tree
-        e2e_h2d = per[0].h2d_bytes + per[0].table_bytes
-        e2e_d2h = per[0].d2h_bytes
+        e2e_h2d, e2e_d2h = mine.h2d_bytes, mine.d2h_bytes
+    d.close()
+    t = time.perf_counter()
+    if w[0] == "pfsp":
+        res1, per1 = bb.pfsp_search(ins, w[2], device=local_rank, M=args.M, **lb2kw(args))
+    else:
+        res1, per1 = bb.nq_search(w[1], 1, device=local_rank, M=args.M)
+    oneshot_t = time.perf_counter() - t
 
-    roof, extra = roofline_objects(bb, w, rec_alg, st.record_bytes, parents, nodes, kernel_ms, iters, lb2_pairs,
-                                   local_rank, args.lb2_pairloop)
+    roof, extra = roofline_objects(bb, w, ins, st.record_bytes, parents, nodes, evals, lb2_evals, kernel_ms, iters,
+                                   lb2_pairs, local_rank, args.lb2_pairloop)
     line = {
         "metric": "explored_nodes_per_sec", "value": value, "unit": "nodes/s", "n_gpus": 1, "steps": K, "warmup": W,
         "ms_per_step": span_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -318,7 +372,13 @@ def run_single(args, w, bb, torch, local_rank):
                    "device_iterations_per_step": iters // K, "grid": st.grid, "smem_bytes": st.smem_bytes},
         "clocks": clocks,
         "e2e": {"value": e2e_nodes / e2e_t, "unit": "nodes/s", "h2d_bytes_per_step": int(e2e_h2d),
-                "d2h_bytes_per_step": int(e2e_d2h)},
+                "d2h_bytes_per_step": int(e2e_d2h),
+                "note": "bb_dist_search on a context opened once per instance (tables resident): reset, root from host "
+                        "memory, search, polls, result; wall clock",
+                "oneshot_value": res1.tree / oneshot_t,
+                "oneshot_note": "bb_pfsp_search / bb_nq_search: engine creation, pool allocation, table upload, LB2 "
+                                "table build, search, teardown; wall clock",
+                "oneshot_h2d_bytes": int(per1[0].h2d_bytes + per1[0].table_bytes)},
         "gpu_launches": int(launches),
         "roofline": roof,
     }
@@ -332,65 +392,88 @@ def run_single(args, w, bb, torch, local_rank):
     print(json.dumps(line), flush=True)
 
 
+def parity_checks(bb, dist, rank, world, local_rank, tag):
+    """untimed, N > 1 only: N-Queens and PFSP whole searches and a -u 0 search across all ranks (work stealing and
+    incumbent exchange between GPUs) against the reference's counts - evidence that travels with the bench line"""
+    out = {}
+    ins29, ins14 = bb.Instance(inst=29), bb.Instance(inst=14)
+    checks = [("nq:15", lambda nm: bb.nq_search_dist(15, 1, rank, world, nm, device=local_rank, M=1 << 18),
+               lambda r: (r.tree, r.sol) == (171129071, 2279184)),
+              ("pfsp:29:2", lambda nm: bb.pfsp_search_dist(ins29, 2, rank, world, nm, device=local_rank, M=1 << 18),
+               lambda r: (r.tree, r.sol, r.best) == (KNOWN_TREES.get(("pfsp", 29, 2), 9499307), 0, 2237)),
+              ("pfsp:14:1 -u 0 (optimum only)",
+               lambda nm: bb.pfsp_search_dist(ins14, 1, rank, world, nm, best0=bb.INT_MAX, device=local_rank, M=1 << 16),
+               lambda r: r.best == 1377 and r.sol >= 1)]
+    for i, (name, call, ok) in enumerate(checks):
+        res, _ = call(f"{tag}_pc{i}")
+        out[name] = "ok" if ok(res) else f"MISMATCH tree={res.tree} sol={res.sol} best={res.best}"
+        dist.barrier()
+    return out
+
+
 def run_multi(args, w, bb, torch, rank, world, local_rank):
-    """one rank per GPU (torchrun): bb_*_search_dist - every step is a whole search shared by all ranks (strong
-    scaling): common warm-up, hash partition, peer-memory work stealing over NVLink, termination detection"""
+    """one rank per GPU (torchrun): every step is a whole search shared by all ranks (strong scaling) on a team
+    context opened once (bb_*_dist_open): common warm-up from the root, device-side hash partition, peer-memory work
+    stealing over NVLink, termination detection. No data-path collective."""
     import torch.distributed as dist
     dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     K, W = args.steps, max(args.warmup, 0)
     ins = bb.Instance(inst=w[1]) if w[0] == "pfsp" else None
-    rec_alg = (ins.n + 2 + 4 * ins.m) if ins else w[1] + 1
-    tag = [f"/bbgpu_{os.getpid()}_{int(time.time() * 1e3) & 0xffffff}"]
+    tag = [shm_tag()]
     dist.broadcast_object_list(tag, src=0)
-
-    def one_step(i):
-        name = f"{tag[0]}_{i}"
-        if w[0] == "pfsp":
-            return bb.pfsp_search_dist(ins, w[2], rank, world, name, device=local_rank, M=args.M, **lb2kw(args))
-        return bb.nq_search_dist(w[1], 1, rank, world, name, device=local_rank, M=args.M)
-
+    checks = parity_checks(bb, dist, rank, world, local_rank, tag[0]) if not args.no_parity_checks else None
+    t_open = time.perf_counter()
+    d = open_dist(bb, w, ins, rank, world, tag[0] + "_team", local_rank, args)
+    open_s = time.perf_counter() - t_open
     for i in range(W):
-        res, mine = one_step(i)
+        res, mine = d.search()
     dist.barrier()
     torch.cuda.synchronize()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
-    search_s = call_s = 0.0
+    search_s = call_s = warm_s = 0.0
     acc = dict(nodes=0, launches=0, parents=0, iters=0, lb2_pairs=0, lb2_evals=0, evals=0, kernel_ms=0.0, h2d=0,
                d2h=0, steals=0, moved=0)
+    busy = []
     t_all = time.perf_counter()
     for i in range(K):
         t = time.perf_counter()
-        res, mine = one_step(W + i)
+        res, mine = d.search()
         dt = time.perf_counter() - t
-        search_s += res.search_s  # already the max over ranks (computed inside the library from every rank's span)
+        search_s += res.search_s  # max over ranks of the root-to-termination span, taken inside the library
+        warm_s += res.warm_s
         tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         call_s += float(tt.item())
         acc["nodes"] += res.tree
         acc["steals"] += res.steals_ok
         acc["moved"] += res.nodes_moved
-        loc = torch.tensor([mine.launches + 6, mine.parents, mine.iterations, mine.lb2_pairs, mine.lb2_evals,
-                            mine.evals, mine.h2d_bytes + mine.table_bytes, mine.d2h_bytes], dtype=torch.int64,
-                           device="cuda")
+        loc = torch.tensor([mine.launches + 8, mine.parents, mine.iterations, mine.lb2_pairs, mine.lb2_evals,
+                            mine.evals, mine.h2d_bytes, mine.d2h_bytes], dtype=torch.int64, device="cuda")
         dist.all_reduce(loc)
         for k, v in zip(("launches", "parents", "iters", "lb2_pairs", "lb2_evals", "evals", "h2d", "d2h"), loc.tolist()):
             acc[k] += v
-        km = torch.tensor([mine.kernel_ms], dtype=torch.float64, device="cuda")
+        km = torch.zeros(world, dtype=torch.float64, device="cuda")
+        km[rank] = mine.kernel_ms
         dist.all_reduce(km)
-        acc["kernel_ms"] += float(km.item())  # sum over ranks: GPU-time spent in expand kernels
+        acc["kernel_ms"] += float(km.sum().item())  # sum over ranks: GPU-time spent in expand kernels
+        busy.append([float(x) / (res.search_s * 1e3) for x in km.tolist()])
     dist.barrier()
     torch.cuda.synchronize()
     wall = time.perf_counter() - t_all
     clocks = sampler.stop() if sampler else None
+    d.close()
     exp = KNOWN_TREES.get(w)
     if exp is not None and res.tree != exp:
         raise SystemExit(f"PARITY FAILURE: explored tree {res.tree} != reference {exp}")
+    if checks and any(v != "ok" for v in checks.values()):
+        raise SystemExit(f"PARITY FAILURE in the untimed multi-GPU checks: {checks}")
     if rank == 0:
         # per-kernel roofline: all ranks' algorithmic bytes over all ranks' kernel time = the average GPU's rate
-        roof, extra = roofline_objects(bb, w, rec_alg, mine.record_bytes, acc["parents"], acc["nodes"],
-                                       acc["kernel_ms"], acc["iters"], acc["lb2_pairs"], local_rank, args.lb2_pairloop)
+        roof, extra = roofline_objects(bb, w, ins, mine.record_bytes, acc["parents"], acc["nodes"], acc["evals"],
+                                       acc["lb2_evals"], acc["kernel_ms"], acc["iters"], acc["lb2_pairs"], local_rank,
+                                       args.lb2_pairloop)
         roof["note_multi"] = "per-GPU average: bytes of all ranks / expand-kernel time summed over ranks"
         line = {
             "metric": "explored_nodes_per_sec", "value": acc["nodes"] / search_s, "unit": "nodes/s", "n_gpus": world,
@@ -399,23 +482,30 @@ def run_multi(args, w, bb, torch, rank, world, local_rank):
             "data": "synthetic (Taillard LCG instance / root board generated in-process)",
             "config": {"workload": workload_name(w), "M": args.M, "tree_nodes": res.tree, "solutions": res.sol,
                        "optimum": res.best if w[0] == "pfsp" else None,
-                       "parallelism": f"search-tree partition over {world} GPUs: hash split of the warm-up pool + "
-                                      "peer-memory work stealing (CUDA IPC over NVLink), no data-path collective",
+                       "parallelism": f"search-tree partition over {world} GPUs: hash split of the common warm-up pool "
+                                      "(on the device) + peer-memory work stealing (CUDA IPC over NVLink), no "
+                                      "data-path collective",
                        "l2": "no flush needed: each step streams the node pool through HBM, far more than the 126 MB L2",
-                       "timing": "per step: max over ranks of the span from the common start barrier (pools seeded, "
-                                 "tables resident) to global termination, taken inside the library on every rank",
+                       "timing": "per step: max over ranks of the device-event span from just before the ROOT is "
+                                 "seeded (reset, root, warm-up, partition) to the detection of global termination, "
+                                 "taken inside the library on every rank",
                        "time_to_optimum_s": search_s / K, "wall_s_per_step": wall / K,
+                       "warm_up_s_per_step": warm_s / K, "team_open_s": open_s,
+                       "gpu_busy_fraction_per_rank": [sum(b[r] for b in busy) / len(busy) for r in range(world)],
                        "steals_per_step": acc["steals"] / K, "nodes_moved_per_step": acc["moved"] / K,
                        "device_iterations_per_step": acc["iters"] // K, "grid": mine.grid,
                        "smem_bytes": mine.smem_bytes},
             "clocks": clocks,
             "e2e": {"value": acc["nodes"] / call_s, "unit": "nodes/s", "h2d_bytes_per_step": int(acc["h2d"] // K),
                     "d2h_bytes_per_step": int(acc["d2h"] // K),
-                    "note": "the bb_*_search_dist call itself with host tables: engine creation, pool cudaMalloc, "
-                            "table upload, IPC exchange, search, teardown; max over ranks"},
+                    "note": "bb_dist_search on a team context opened once per instance (tables resident, peers' "
+                            "transfer buffers mapped): reset, root from host memory, warm-up, search, polls, result; "
+                            "wall clock, max over ranks"},
             "gpu_launches": int(acc["launches"]),
             "roofline": roof,
         }
+        if checks is not None:
+            line["parity_checks"] = checks
         line.update(extra)
         if not args.no_cpu_baseline:
             line["cpu_baseline"] = None  # measured at N=1 only (bench contract)
@@ -436,6 +526,8 @@ def main():
                          "that per GPU on several")
     ap.add_argument("--ref-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity-checks", action="store_true",
+                    help="N > 1: skip the untimed N-Queens / PFSP / -u 0 multi-GPU parity searches")
     ap.add_argument("--lb2-pairloop", action="store_true",
                     help="LB2 through the staged machine-pair loop (integer-ALU bound) instead of the subset table")
     args = ap.parse_args()
