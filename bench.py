@@ -438,6 +438,8 @@ def run_multi(args, w, bb, torch, rank, world, local_rank):
     busy = []
     t_all = time.perf_counter()
     for i in range(K):
+        dist.barrier()  # ranks enter the timed call together (the reductions below skew them otherwise)
+        torch.cuda.synchronize()
         t = time.perf_counter()
         res, mine = d.search()
         dt = time.perf_counter() - t
@@ -522,8 +524,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="pfsp:21:2")
     ap.add_argument("--M", type=int, default=0,
-                    help="max parents per device iteration (-M); 0 = 2 M (PFSP) / 4 M (N-Queens) on one GPU, half of "
-                         "that per GPU on several")
+                    help="max parents per device iteration (-M); 0 = 2 M (PFSP) / 4 M (N-Queens) per GPU")
     ap.add_argument("--ref-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity-checks", action="store_true",
@@ -535,7 +536,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.M <= 0:
-        args.M = (1 << 21 if w[0] == "pfsp" else 1 << 22) >> (1 if world > 1 else 0)
+        args.M = 1 << 21 if w[0] == "pfsp" else 1 << 22
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":

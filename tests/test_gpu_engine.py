@@ -241,3 +241,22 @@ def test_pfsp_full_size_properties():
     res, per = bb.pfsp_search(ins, 0, M=1 << 20)
     assert (res.tree, res.sol, res.best) == (711291688, 4346, 2099)
     assert per[0].parents == res.tree + 1
+
+
+def test_persistent_context_searches_repeat():
+    """bb_*_dist_open / bb_dist_search / bb_dist_close with a team of one: several searches on one context give the
+    reference's counts every time (nothing of a finished search leaks into the next), timed from the root"""
+    import os
+    d = bb.Dist(0, 1, f"/bbtest_{os.getpid()}_a", instance=bb.Instance(inst=14), lb=2, M=1 << 16)
+    for _ in range(3):
+        res, mine = d.search()
+        assert (res.tree, res.sol, res.best) == (144639, 0, 1377)
+        assert res.search_s > 0 and mine.parents + 0 >= 1
+    res, _ = d.search(best0=INT_MAX)  # -u 0 on the same context
+    assert res.best == 1377 and res.sol >= 1
+    d.close()
+    d = bb.Dist(0, 1, f"/bbtest_{os.getpid()}_b", N=13, G=1, M=1 << 18)
+    for _ in range(2):
+        res, _ = d.search()
+        assert (res.tree, res.sol) == (4674889, 73712)
+    d.close()
