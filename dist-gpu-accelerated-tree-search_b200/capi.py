@@ -100,7 +100,7 @@ EXPORTS = [
     "bytes_per_inv_lb1", "flop_lb2", "bytes_per_inv_lb2", "nq_evaluate_gpu", "bb_taillard_nb_jobs",
     "bb_taillard_nb_machines", "bb_taillard_best_ub", "bb_taillard_seed", "bb_taillard_processing_times",
     "bb_pfsp_instance_taillard", "bb_pfsp_instance_from_ptimes", "bb_pfsp_instance_free", "bb_config_default",
-    "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_engine_reset", "bb_engine_push_root",
+    "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_release_cached_memory", "bb_engine_reset", "bb_engine_push_root",
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
     "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist", "bb_pfsp_dist_open", "bb_nq_dist_open", "bb_dist_search",
     "bb_dist_close",
@@ -122,6 +122,7 @@ lib.bb_pfsp_engine_create.argtypes = [C.POINTER(PfspInstance), C.c_int, C.POINTE
 lib.bb_nq_engine_create.restype = _vp
 lib.bb_nq_engine_create.argtypes = [C.c_int, C.c_int, C.POINTER(Config)]
 lib.bb_engine_destroy.argtypes = [_vp]
+lib.bb_release_cached_memory.argtypes = [C.c_int]
 lib.bb_engine_reset.argtypes = [_vp, C.c_int]
 lib.bb_engine_push_root.argtypes = [_vp]
 lib.bb_engine_push_nodes.argtypes = [_vp, _vp, C.c_int]

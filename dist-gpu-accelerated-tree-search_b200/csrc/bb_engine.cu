@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 /* ------------------------------------------------------------------ errors */
@@ -390,22 +391,58 @@ __global__ void k_export_nq3(uint8_t *__restrict__ nodes, bb_pool pool, int stac
 
 /* ------------------------------------------------------------------ creation */
 
-/* The node stacks and the LB2 table come from the device's stream-ordered allocator with an unlimited release
- * threshold: the first engine of a process pays cudaMalloc-class cost for its multi-GB pool, later engines on the
- * same GPU (one search after another, which is how the library is used) get the cached blocks back in microseconds.
- * The memory returns to the driver at process exit. */
-static int pool_alloc(bb_engine *e, void **ptr, size_t bytes)
+/* The node stacks and the LB2 table come from a stream-ordered memory pool that BELONGS TO THIS LIBRARY (one per
+ * device, created on first use, unlimited release threshold): the first engine of a process pays cudaMalloc-class
+ * cost for its multi-GB pool, later engines on the same GPU (one search after another, which is how the library is
+ * used) get the cached blocks back in microseconds. The device's default pool - which the embedding application and
+ * other libraries share - is left alone, and bb_release_cached_memory() hands the cached blocks back to the driver. */
+static cudaMemPool_t g_mempool[64];
+static std::mutex g_mempool_mutex;
+
+static int library_pool(int device, cudaMemPool_t *out)
 {
-  static thread_local unsigned long long configured = 0ull; /* bit per device ordinal < 64 */
-  if (e->device < 64 && !((configured >> e->device) & 1ull))
+  if (device < 0 || device >= 64)
+    return bb_fail(BB_ERR_ARG, "device ordinal %d not supported (max 63)", device);
+  std::lock_guard<std::mutex> lock(g_mempool_mutex);
+  if (!g_mempool[device])
   {
+    cudaMemPoolProps props;
+    memset(&props, 0, sizeof(props));
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
     cudaMemPool_t mp;
-    BB_CUDA_TRY(cudaDeviceGetDefaultMemPool(&mp, e->device));
+    BB_CUDA_TRY(cudaMemPoolCreate(&mp, &props));
     unsigned long long keep = ~0ull;
     BB_CUDA_TRY(cudaMemPoolSetAttribute(mp, cudaMemPoolAttrReleaseThreshold, &keep));
-    configured |= 1ull << e->device;
+    g_mempool[device] = mp;
   }
-  BB_CUDA_TRY(cudaMallocAsync(ptr, bytes, e->stream));
+  *out = g_mempool[device];
+  return BB_OK;
+}
+
+static int pool_alloc(bb_engine *e, void **ptr, size_t bytes)
+{
+  cudaMemPool_t mp;
+  const int rc = library_pool(e->device, &mp);
+  if (rc)
+    return rc;
+  BB_CUDA_TRY(cudaMallocFromPoolAsync(ptr, bytes, mp, e->stream));
+  return BB_OK;
+}
+
+extern "C" int bb_release_cached_memory(int device)
+{
+  if (device < 0 || device >= 64)
+    return bb_fail(BB_ERR_ARG, "device ordinal %d not supported (max 63)", device);
+  std::lock_guard<std::mutex> lock(g_mempool_mutex);
+  if (g_mempool[device])
+  {
+    BB_CUDA_TRY(cudaSetDevice(device));
+    BB_CUDA_TRY(cudaDeviceSynchronize());
+    BB_CUDA_TRY(cudaMemPoolTrimTo(g_mempool[device], 0));
+  }
   return BB_OK;
 }
 
@@ -973,8 +1010,10 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
       if (nd[(size_t)i * (1 + BB_MAX_QUEENS)] >= e->N)
         return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * (1 + BB_MAX_QUEENS)], e->N - 1);
   }
-  void *stage = nullptr;
-  BB_CUDA_TRY(cudaMalloc(&stage, rec * count));
+  void *stage = nullptr; /* from the library's stream-ordered pool: no device-wide synchronisation per call */
+  rc = pool_alloc(e, &stage, rec * count);
+  if (rc)
+    return rc;
   cudaError_t err = cudaMemcpyAsync(stage, host_nodes, rec * count, cudaMemcpyHostToDevice, e->stream);
   e->h2d_bytes += rec * count;
   if (err == cudaSuccess)
@@ -990,9 +1029,9 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
     k_plan<<<1, 1, 0, e->stream>>>(e->ctrl, count, e->grid * (e->threads / 32));
     err = cudaGetLastError();
   }
+  pool_free(e, stage);
   if (err == cudaSuccess)
     err = cudaStreamSynchronize(e->stream);
-  cudaFree(stage);
   if (err != cudaSuccess)
     return bb_fail_cuda(err, "seeding", __FILE__, __LINE__);
   return BB_OK;
@@ -1035,7 +1074,9 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     return 0;
   const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
   void *stage = nullptr;
-  BB_CUDA_TRY(cudaMalloc(&stage, rec * total));
+  rc = pool_alloc(e, &stage, rec * total);
+  if (rc)
+    return rc;
   int at = 0;
   for (int s = 0; s < 2; s++)
   {
@@ -1054,9 +1095,9 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
   cudaError_t err = cudaGetLastError();
   if (err == cudaSuccess)
     err = cudaMemcpyAsync(host_nodes, stage, rec * total, cudaMemcpyDeviceToHost, e->stream);
+  pool_free(e, stage);
   if (err == cudaSuccess)
     err = cudaStreamSynchronize(e->stream);
-  cudaFree(stage);
   if (err != cudaSuccess)
     return bb_fail_cuda(err, "export", __FILE__, __LINE__);
   return total;

@@ -203,6 +203,11 @@ bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb, const bb_c
 bb_engine *bb_nq_engine_create(int N, int G, const bb_config *cfg);
 void bb_engine_destroy(bb_engine *e);
 
+/* Pools and LB2 tables of destroyed engines stay cached in a memory pool owned by this library (so that the next
+ * engine on the same GPU does not pay the allocation again); this returns the cached blocks of `device` to the driver.
+ * The device's default memory pool, which other code in the process may use, is never touched. */
+int bb_release_cached_memory(int device);
+
 int bb_engine_reset(bb_engine *e, int best);            /* empty pool, zero counters, set incumbent */
 int bb_engine_push_root(bb_engine *e);                  /* initRoot: PFSP_node.c:7-14 / NQueens_node.c:7-13 */
 /* Seed from HOST nodes in the reference's AoS layouts (Node / bb_nq_node); the engine derives its cached
