@@ -60,7 +60,9 @@ int orc_lb2_census(const orc_pfsp *t, const int *prmu, int limit1, int limit2, i
 
 /* ---- batch level: the reference's chunk protocol ---- */
 /* Node records are flat int16: [depth, limit1, prmu[ORC_MAX_JOBS]] = the reference's 44-byte Node. */
+#ifndef ORC_MAX_JOBS /* liboracle50.so is this same code built with -DORC_MAX_JOBS=50 (the 50-job Taillard classes) */
 #define ORC_MAX_JOBS 20
+#endif
 #define ORC_NODE_I16 (2 + ORC_MAX_JOBS)
 /* nodeIndex/sumOffSets construction, pfsp_multigpu_cuda.c:275-283. returns numBounds */
 int orc_batch_index(const int16_t *parents, int nparents, int jobs, int *sum_offsets, int *node_index);

@@ -36,14 +36,14 @@ def build_oracle(ref=False):
         subprocess.run(["make", "-C", ORACLE_DIR, "-s", "ref"], check=True, stderr=subprocess.DEVNULL)
 
 
-_oracle = None
+_oracle = {}
 
 
-def oracle():
-    global _oracle
-    if _oracle is not None:
-        return _oracle
-    path = os.path.join(ORACLE_DIR, "liboracle.so")
+def oracle(max_jobs=20):
+    """the CPU checker; max_jobs = 50 loads the same code built with 50-job node records (liboracle50.so)"""
+    if max_jobs in _oracle:
+        return _oracle[max_jobs]
+    path = os.path.join(ORACLE_DIR, "liboracle.so" if max_jobs == 20 else f"liboracle{max_jobs}.so")
     if not os.path.exists(path):
         build_oracle()
     L = C.CDLL(path)
@@ -71,7 +71,8 @@ def oracle():
     L.orc_nq_labels.argtypes = [C.c_int, C.c_int, u8p, C.c_int, u8p]
     L.orc_nq_generate_children.argtypes = [C.c_int, u8p, C.c_int, u8p, ullp, ullp, u8p]
     L.orc_nq_search.argtypes = [C.c_int, C.c_int, C.c_longlong, C.POINTER(RunStats)]
-    _oracle = L
+    L.node_i16 = 2 + max_jobs
+    _oracle[max_jobs] = L
     return L
 
 
@@ -79,14 +80,18 @@ def have_ref():
     return os.path.exists(os.path.join(REF_DIR, "libref_pfsp.so"))
 
 
-_ref_pfsp = None
+_ref_pfsp = {}
 _ref_nq = None
 
 
-def ref_pfsp():
-    global _ref_pfsp
-    if _ref_pfsp is None:
-        L = C.CDLL(os.path.join(REF_DIR, "libref_pfsp.so"))
+def have_ref50():
+    return os.path.exists(os.path.join(REF_DIR, "libref_pfsp50.so"))
+
+
+def ref_pfsp(max_jobs=20):
+    """the compiled reference; max_jobs = 50 is the build with MAX_JOBS edited to 50 (make -C oracle ref50)"""
+    if max_jobs not in _ref_pfsp:
+        L = C.CDLL(os.path.join(REF_DIR, "libref_pfsp.so" if max_jobs == 20 else f"libref_pfsp{max_jobs}.so"))
         L.ref_pfsp_open.restype = C.c_void_p
         L.ref_pfsp_open.argtypes = [C.c_int]
         L.ref_pfsp_close.argtypes = [C.c_void_p]
@@ -100,8 +105,9 @@ def ref_pfsp():
         L.ref_pfsp_search.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), ullp, ullp, C.c_longlong]
         L.ref_pfsp_decompose.argtypes = [C.c_void_p, C.c_int, i16p, C.c_int, C.POINTER(C.c_int), ullp, ullp, i16p]
         L.ref_generate_children.argtypes = [i16p, C.c_int, C.c_int, i32p, ullp, ullp, C.POINTER(C.c_int), i16p]
-        _ref_pfsp = L
-    return _ref_pfsp
+        L.node_i16 = 2 + max_jobs
+        _ref_pfsp[max_jobs] = L
+    return _ref_pfsp[max_jobs]
 
 
 def ref_nq():
@@ -162,10 +168,10 @@ def fnv(a):
     return int(oracle().orc_fnv1a_i32(a, a.size))
 
 
-def random_pfsp_nodes(rng, n, count, min_depth=0, max_depth=None):
-    """random partial permutations as flat reference Node records [depth, limit1, prmu[20]]"""
+def random_pfsp_nodes(rng, n, count, min_depth=0, max_depth=None, width=NODE_I16):
+    """random partial permutations as flat reference Node records [depth, limit1, prmu[MAX_JOBS]]"""
     max_depth = n - 1 if max_depth is None else max_depth
-    out = np.zeros((count, NODE_I16), dtype=np.int16)
+    out = np.zeros((count, width), dtype=np.int16)
     for i in range(count):
         d = int(rng.integers(min_depth, max_depth + 1))
         out[i, 0] = d
@@ -183,15 +189,15 @@ def random_nq_nodes(rng, N, count, min_depth=0, max_depth=None):
     return out
 
 
-def oracle_one_level(inst_handle, n, lb, parents, best):
+def oracle_one_level(inst_handle, n, lb, parents, best, L=None):
     """one batch through the oracle: evaluate_gpu's bounds[] (orc_evaluate_chunk) then generate_children
     (PFSP_lib.h:51-95). Returns (children, tree increment, sol increment, incumbent, child bounds evaluated)."""
-    L = oracle()
+    L = L or oracle()
     parents = np.ascontiguousarray(parents, dtype=np.int16)
     nb = int((n - parents[:, 0]).sum())
     bounds = np.zeros(max(nb, 1), np.int32)
     L.orc_evaluate_chunk(inst_handle, lb, parents, len(parents), best, bounds)
     tree, sol, b = C.c_ulonglong(0), C.c_ulonglong(0), C.c_int(best)
-    kids = np.zeros((max(nb, 1), NODE_I16), np.int16)
+    kids = np.zeros((max(nb, 1), L.node_i16), np.int16)
     k = L.orc_generate_children(parents, len(parents), n, bounds, C.byref(tree), C.byref(sol), C.byref(b), kids)
     return kids[:k], tree.value, sol.value, b.value, nb
