@@ -10,6 +10,8 @@ LIB_PATH = os.path.join(_HERE, "libbbgpu.so")
 MAX_JOBS = 20
 MAX_MACHINES = 20
 MAX_QUEENS = 20
+MAX_JOBS_WIDE = 50
+NODE_I16_WIDE = 2 + MAX_JOBS_WIDE  # the reference's Node when built with MAX_JOBS 50 (engines of 21..50-job instances)
 NODE_I16 = 2 + MAX_JOBS     # reference PFSP Node: int16 depth, limit1, prmu[20]  (pfsp/lib/PFSP_node.h:15-20)
 NQ_REC = 1 + MAX_QUEENS     # reference N-Queens Node: uint8 depth, board[20]     (nqueens/lib/NQueens_node.h:13-17)
 INT_MAX = 2**31 - 1
@@ -236,6 +238,7 @@ class Engine:
     def pfsp(cls, instance, lb, **cfg):
         e = cls(lib.bb_pfsp_engine_create(instance.ptr, lb, C.byref(default_config(**cfg))), "pfsp")
         e.instance = instance  # keep the host tables alive
+        e.node_i16 = NODE_I16_WIDE if instance.n > MAX_JOBS else NODE_I16
         return e
 
     @classmethod
@@ -249,12 +252,12 @@ class Engine:
         check(lib.bb_engine_push_root(self.h), "bb_engine_push_root")
 
     def push_nodes(self, nodes):
-        dt, w = (np.int16, NODE_I16) if self.kind == "pfsp" else (np.uint8, NQ_REC)
+        dt, w = (np.int16, getattr(self, "node_i16", NODE_I16)) if self.kind == "pfsp" else (np.uint8, NQ_REC)
         a = np.ascontiguousarray(nodes, dtype=dt).reshape(-1, w)
         check(lib.bb_engine_push_nodes(self.h, a.ctypes.data, a.shape[0]), "bb_engine_push_nodes")
 
     def export_nodes(self, max_count=1 << 22):
-        dt, w = (np.int16, NODE_I16) if self.kind == "pfsp" else (np.uint8, NQ_REC)
+        dt, w = (np.int16, getattr(self, "node_i16", NODE_I16)) if self.kind == "pfsp" else (np.uint8, NQ_REC)
         st = self.stats()
         cnt = max(int(st.pool_size), 1)
         if cnt > max_count:

@@ -14,6 +14,7 @@
 #include "bb_pfsp_lb2.cuh"
 #include "bb_pfsp_packed.cuh"
 #include "bb_pfsp_tpp.cuh"
+#include "bb_pfsp_wide.cuh"
 
 #include <climits>
 #include <cstdarg>
@@ -94,6 +95,10 @@ struct bb_engine
   void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
+  /* PFSP, 21..50 jobs (bb_pfsp_wide.cuh): wider record, its own tables */
+  int wide;
+  bb_pfsp_wide_dev TW;
+  void *wide_mem;
   /* N-Queens */
   int N, G;
   int nq_gen; /* 3 = masks travel with the node (nq_expand3, 32-byte record), 2 / 1 = earlier kernels (board + depth) */
@@ -303,6 +308,71 @@ __global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int sta
   nd[0] = (int16_t)depth;
   nd[1] = (int16_t)(depth - 1);
   for (int j = 0; j < BB_MAX_JOBS; j++)
+    nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
+}
+
+/* 21..50 jobs: the reference's Node built with MAX_JOBS 50 (int16 depth, limit1, prmu[50]) <-> the wide record */
+__global__ void k_seed_pfsp_wide(const int16_t *__restrict__ nodes, int count, bb_pool pool, bb_pfsp_wide_dev T, int at)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  const int16_t *nd = nodes + (size_t)i * (2 + BB_WIDE_JOBS);
+  const int depth = nd[0];
+  uint32_t w[BB_WIDE_PLANES * 4];
+  for (int q = 0; q < BB_WIDE_PLANES * 4; q++)
+    w[q] = 0;
+  unsigned long long mask = 0;
+  int front[BB_MAX_MACHINES], remain[BB_MAX_MACHINES];
+  for (int k = 0; k < T.m; k++)
+    front[k] = remain[k] = 0;
+  for (int j = 0; j < T.n; j++)
+  {
+    const int job = nd[2 + j] & 0xff;
+    w[j >> 2] |= (uint32_t)job << (8 * (j & 3));
+    if (j < depth)
+    {
+      mask |= 1ull << job;
+      front[0] += T.p8[job];
+      for (int k = 1; k < T.m; k++)
+        front[k] = max(front[k - 1], front[k]) + T.p8[k * BB_WIDE_STRIDE + job];
+    }
+    else
+      for (int k = 0; k < T.m; k++)
+        remain[k] += T.p8[k * BB_WIDE_STRIDE + job];
+  }
+  w[BB_WIDE_W_DEPTH] = (uint32_t)depth;
+  w[BB_WIDE_W_MASK] = (uint32_t)mask;
+  w[BB_WIDE_W_MASK + 1] = (uint32_t)(mask >> 32);
+  uint16_t *h = reinterpret_cast<uint16_t *>(w);
+  for (int k = 0; k < T.m; k++)
+  {
+    h[2 * BB_WIDE_W_FRONT + k] = (uint16_t)front[k];
+    h[2 * BB_WIDE_W_REMAIN + k] = (uint16_t)remain[k];
+  }
+  for (int q = 0; q < BB_WIDE_PLANES; q++)
+    pool.planes[0][(size_t)q * pool.capacity + at + i] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+}
+
+__global__ void k_export_pfsp_wide(int16_t *__restrict__ nodes, bb_pool pool, int stack, int from, int count, int out_at)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count)
+    return;
+  uint32_t w[16];
+  for (int q = 0; q < 4; q++)
+  {
+    const uint4 v = pool.planes[stack][(size_t)q * pool.capacity + from + i];
+    w[4 * q] = v.x;
+    w[4 * q + 1] = v.y;
+    w[4 * q + 2] = v.z;
+    w[4 * q + 3] = v.w;
+  }
+  int16_t *nd = nodes + (size_t)(out_at + i) * (2 + BB_WIDE_JOBS);
+  const int depth = w[BB_WIDE_W_DEPTH] & 0xff;
+  nd[0] = (int16_t)depth;
+  nd[1] = (int16_t)(depth - 1);
+  for (int j = 0; j < BB_WIDE_JOBS; j++)
     nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
 }
 
@@ -533,7 +603,12 @@ static int setup_launch(bb_engine *e, const void *kernel, int smem, int threads 
 
 static int launch_expand(bb_engine *e, cudaStream_t s)
 {
-  if (e->kind == KIND_PFSP)
+  if (e->kind == KIND_PFSP && e->wide)
+  {
+    void *args[] = {&e->ctrl, &e->pool, &e->TW, &e->prefilter};
+    BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(e->threads), args, e->smem, s));
+  }
+  else if (e->kind == KIND_PFSP)
   {
     void *args[] = {&e->ctrl, &e->pool, &e->T, &e->prefilter, &e->stage_a};
     BB_CUDA_TRY(cudaLaunchKernel(e->kernel, dim3(e->grid), dim3(e->threads), args, e->smem, s));
@@ -716,8 +791,78 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   return BB_OK;
 }
 
+/* 21..50 jobs: tables of bb_pfsp_wide_dev in one allocation, the wide kernel of the requested bound */
+static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
+{
+  e->kind = KIND_PFSP;
+  e->wide = 1;
+  e->lb = lb;
+  e->n = ins->nb_jobs;
+  e->m = ins->nb_machines;
+  e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
+  int rc = alloc_common(e, cfg, BB_WIDE_PLANES, 0);
+  if (rc)
+    return rc;
+  const int n = e->n, m = e->m, P = ins->nb_machine_pairs > 0 ? ins->nb_machine_pairs : 0, P1 = P > 0 ? P : 1;
+  const size_t sz_p8 = (size_t)m * BB_WIDE_STRIDE, sz_tails = ((size_t)m * 4 + 15) & ~(size_t)15;
+  const size_t sz_jjob = (size_t)P1 * BB_WIDE_STRIDE, sz_int = (size_t)P1 * BB_WIDE_STRIDE * 4, sz_pairs = (size_t)P1 * 8;
+  const size_t o_tails = (sz_p8 + 15) & ~(size_t)15, o_jjob = o_tails + sz_tails, o_ja = (o_jjob + sz_jjob + 15) & ~(size_t)15;
+  const size_t o_jb = o_ja + sz_int, o_pairs = o_jb + sz_int, total = o_pairs + sz_pairs;
+  std::vector<unsigned char> h(total, 0);
+  for (int k = 0; k < m; k++)
+  {
+    for (int j = 0; j < n; j++)
+    {
+      const int v = ins->p_times[k * n + j];
+      if (v < 0 || v > 255)
+        return bb_fail(BB_ERR_ARG, "processing time %d out of the supported 0..255 range", v);
+      h[(size_t)k * BB_WIDE_STRIDE + j] = (unsigned char)v;
+    }
+    ((int *)(h.data() + o_tails))[k] = ins->min_tails[k];
+  }
+  memset(h.data() + o_jjob, 0xff, sz_jjob);
+  for (int l = 0; l < P; l++)
+  {
+    const int sidx = ins->machine_pair_order[l];
+    const int m1 = ins->machine_pairs_1[sidx], m2 = ins->machine_pairs_2[sidx];
+    ((int2 *)(h.data() + o_pairs))[l] = make_int2(m1, m2);
+    for (int q = 0; q < n; q++)
+    {
+      const int job = ins->johnson_schedules[sidx * n + q];
+      h[o_jjob + (size_t)l * BB_WIDE_STRIDE + q] = (unsigned char)job;
+      ((int *)(h.data() + o_ja))[(size_t)l * BB_WIDE_STRIDE + q] = ins->p_times[m2 * n + job] - ins->p_times[m1 * n + job];
+      ((int *)(h.data() + o_jb))[(size_t)l * BB_WIDE_STRIDE + q] = ins->lags[sidx * n + job] + ins->p_times[m2 * n + job];
+    }
+  }
+  BB_CUDA_TRY(cudaMalloc(&e->wide_mem, total));
+  BB_CUDA_TRY(cudaMemcpy(e->wide_mem, h.data(), total, cudaMemcpyHostToDevice));
+  e->table_bytes = total;
+  unsigned char *d = (unsigned char *)e->wide_mem;
+  e->TW.n = n;
+  e->TW.m = m;
+  e->TW.P = P;
+  e->TW.p8 = d;
+  e->TW.tails = (const int *)(d + o_tails);
+  e->TW.jjob = d + o_jjob;
+  e->TW.ja = (const int *)(d + o_ja);
+  e->TW.jb = (const int *)(d + o_jb);
+  e->TW.pairs = (const int2 *)(d + o_pairs);
+  e->T.n = n; /* the generic code paths read n / m from here */
+  e->T.m = m;
+  e->T.P = P;
+  const void *k = lb == 0   ? (const void *)bbk::pfsp_expand_wide<0>
+                  : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1>
+                            : (const void *)bbk::pfsp_expand_wide<2>;
+  rc = setup_launch(e, k, bbk::wide_layout(m).total);
+  if (rc)
+    return rc;
+  return build_graph(e);
+}
+
 static int create_pfsp(bb_engine *e, const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
 {
+  if (ins->nb_jobs > BB_MAX_JOBS)
+    return create_pfsp_wide(e, ins, lb, cfg);
   e->kind = KIND_PFSP;
   e->lb = lb;
   e->n = ins->nb_jobs;
@@ -839,11 +984,11 @@ extern "C" bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb,
     bb_fail(BB_ERR_ARG, "bb_pfsp_engine_create: bad instance or lower bound %d", lb);
     return nullptr;
   }
-  if (ins->nb_jobs > BB_MAX_JOBS || ins->nb_machines > BB_MAX_MACHINES)
+  if (ins->nb_jobs > BB_WIDE_JOBS || ins->nb_machines > BB_MAX_MACHINES)
   {
     /* the reference needs a rebuild with a larger MAX_JOBS for these (pfsp/README.md:52); refuse loudly */
     bb_fail(BB_ERR_ARG, "instance has %d jobs x %d machines; this build supports at most %d x %d", ins->nb_jobs,
-            ins->nb_machines, BB_MAX_JOBS, BB_MAX_MACHINES);
+            ins->nb_machines, BB_WIDE_JOBS, BB_MAX_MACHINES);
     return nullptr;
   }
   bb_engine *e = (bb_engine *)calloc(1, sizeof(bb_engine));
@@ -916,6 +1061,8 @@ extern "C" void bb_engine_destroy(bb_engine *e)
   }
   if (e->table_mem)
     cudaFree(e->table_mem);
+  if (e->wide_mem)
+    cudaFree(e->wide_mem);
   pool_free(e, e->g16_mem);
   if (e->stream)
     cudaStreamSynchronize(e->stream);
@@ -994,14 +1141,15 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
   const int at = e->ctrl_h->size[0];
   if ((long long)at + count > e->pool.capacity)
     return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while seeding %d nodes", e->pool.capacity, count);
-  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
   if (e->kind == KIND_PFSP)
   {
     /* nodes the engine cannot represent are rejected here rather than silently mis-handled */
     const int16_t *nd = (const int16_t *)host_nodes;
+    const size_t st16 = 2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS);
     for (int i = 0; i < count; i++)
-      if (nd[(size_t)i * (2 + BB_MAX_JOBS)] < 0 || nd[(size_t)i * (2 + BB_MAX_JOBS)] >= e->n)
-        return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * (2 + BB_MAX_JOBS)], e->n - 1);
+      if (nd[(size_t)i * st16] < 0 || nd[(size_t)i * st16] >= e->n)
+        return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * st16], e->n - 1);
   }
   else
   {
@@ -1019,7 +1167,9 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
   if (err == cudaSuccess)
   {
     const int blocks = (count + 127) / 128;
-    if (e->kind == KIND_PFSP)
+    if (e->kind == KIND_PFSP && e->wide)
+      k_seed_pfsp_wide<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
+    else if (e->kind == KIND_PFSP)
       k_seed_pfsp<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->T, at, e->T.mp,
                                                  e->pool.nplanes);
     else if (e->nq_gen == 3)
@@ -1043,7 +1193,7 @@ extern "C" int bb_engine_push_root(bb_engine *e)
     return bb_fail(BB_ERR_ARG, "null engine");
   if (e->kind == KIND_PFSP)
   {
-    int16_t nd[2 + BB_MAX_JOBS];
+    int16_t nd[2 + BB_WIDE_JOBS]; /* a 20-job engine reads the first 2 + 20 entries */
     memset(nd, 0, sizeof(nd));
     nd[0] = 0;
     nd[1] = -1;
@@ -1072,7 +1222,7 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     return bb_fail(BB_ERR_ARG, "export buffer holds %lld nodes, pool has %lld", max_count, total);
   if (total == 0)
     return 0;
-  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + BB_MAX_JOBS) : (1 + BB_MAX_QUEENS);
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
   void *stage = nullptr;
   rc = pool_alloc(e, &stage, rec * total);
   if (rc)
@@ -1084,7 +1234,9 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     if (!cnt)
       continue;
     const int blocks = (cnt + 127) / 128;
-    if (e->kind == KIND_PFSP)
+    if (e->kind == KIND_PFSP && e->wide)
+      k_export_pfsp_wide<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
+    else if (e->kind == KIND_PFSP)
       k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else if (e->nq_gen == 3)
       k_export_nq3<<<blocks, 128, 0, e->stream>>>((uint8_t *)stage, e->pool, s, from, cnt, at, e->N);
@@ -1364,7 +1516,8 @@ int bb_engine_zero_counters(bb_engine *e)
  * the root to the same SET of nodes; it keeps the nodes whose placed prefix hashes to its id and drops the others, in
  * place, stack by stack (one CTA: the warm-up pool is a few thousand nodes). A content hash needs no communication
  * and does not depend on the order in which the device appended the nodes.
- * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4), 2: N-Queens plane + tail words. */
+ * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4), 2: N-Queens plane + tail words, 3: PFSP record
+ * of the 50-job classes. */
 __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, int mode, int nq_dbyte, int D, int me,
                                                    int total_warps)
 {
@@ -1378,7 +1531,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
     for (int c0 = from; c0 < to; c0 += blockDim.x)
     {
       const int i = c0 + threadIdx.x;
-      uint4 pl[7];
+      uint4 pl[BB_WIDE_PLANES];
       uint32_t tw[2] = {0u, 0u};
       bool keep = false;
       if (i < to)
@@ -1387,9 +1540,15 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
           pl[q] = pool.planes[s][(size_t)q * pool.capacity + i];
         for (int t = 0; t < pool.tail_words; t++)
           tw[t] = pool.tailw[s][(size_t)i * pool.tail_words + t];
-        uint32_t w[6] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w, 0u, 0u};
+        uint32_t w[13] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
         int depth;
-        if (mode == 0)
+        if (mode == 3)
+        { /* wide PFSP record: prmu in words 0..12, depth in word 13 */
+          const uint4 a = pl[1], b = pl[2], c4 = pl[3];
+          w[4] = a.x, w[5] = a.y, w[6] = a.z, w[7] = a.w, w[8] = b.x, w[9] = b.y, w[10] = b.z, w[11] = b.w, w[12] = c4.x;
+          depth = (int)(c4.y & 0xffu);
+        }
+        else if (mode == 0)
         {
           w[4] = pl[1].x;
           depth = (int)(pl[1].y & 0xffu);
@@ -1452,7 +1611,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
 int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters)
 {
   ENGINE_SET_DEVICE(e);
-  int mode = 0, dbyte = 0;
+  int mode = e->wide ? 3 : 0, dbyte = 0;
   if (e->kind == KIND_NQ)
   {
     mode = e->nq_gen == 3 ? 1 : 2;

@@ -169,12 +169,12 @@ int main(int argc, char *argv[])
     return EXIT_FAILURE;
   }
   print_settings(inst, ins->nb_machines, ins->nb_jobs, ub, lb, D, C, ws);
-  if (ins->nb_jobs > BB_MAX_JOBS || ins->nb_machines > BB_MAX_MACHINES)
+  if (ins->nb_jobs > BB_MAX_JOBS_WIDE || ins->nb_machines > BB_MAX_MACHINES)
   {
     /* the reference needs a rebuild with a larger MAX_JOBS for these classes (pfsp/README.md:52) and silently
      * overflows otherwise; refuse instead */
     fprintf(stderr, "Error: ta%d has %d jobs x %d machines; this build supports at most %d x %d\n", inst,
-            ins->nb_jobs, ins->nb_machines, BB_MAX_JOBS, BB_MAX_MACHINES);
+            ins->nb_jobs, ins->nb_machines, BB_MAX_JOBS_WIDE, BB_MAX_MACHINES);
     return EXIT_FAILURE;
   }
   const int optimum0 = ub == 1 ? ins->best_known : INT_MAX;

@@ -152,7 +152,10 @@ def oracle_tables(inst):
 
 
 def ref_tables(inst):
-    R = ref_pfsp()
+    return ref_tables_of(ref_pfsp(), inst)
+
+
+def ref_tables_of(R, inst):
     h = R.ref_pfsp_open(inst)
     n, m, P, ub = C.c_int(), C.c_int(), C.c_int(), C.c_int()
     R.ref_pfsp_dims(h, n, m, P, ub)

@@ -38,11 +38,11 @@ def test_pfsp_flag_validation_matches_reference(args, msg, tmp_path):
 def test_pfsp_settings_block_and_refusals(tmp_path):
     r = run(PFSP, "-C", 2, cwd=tmp_path)  # pfsp_multigpu_cuda.c:523-527
     assert r.returncode == 1 and r.stdout.startswith("C is set to 2. Invalid option for this version.")
-    r = run(PFSP, "--inst", 31, "--lb", 0, "--ub", 0, "-C", 0, "-w", 0, cwd=tmp_path)  # 50 jobs: refused loudly
-    assert r.returncode == 1 and "supports at most 20 x 20" in r.stderr
+    r = run(PFSP, "--inst", 61, "--lb", 0, "--ub", 0, "-C", 0, "-w", 0, cwd=tmp_path)  # 100 jobs: refused loudly
+    assert r.returncode == 1 and "supports at most 50 x 20" in r.stderr
     assert r.stdout == ("\n=================================================\n"
                         "Multi-core Multi-GPU C+OpenMP+CUDA (1 GPU(s) - [0] Multi-core - [0] Work Stealing)\n\n"
-                        "Resolution of PFSP Taillard's instance: ta31 (m = 5, n = 50)\n"
+                        "Resolution of PFSP Taillard's instance: ta61 (m = 5, n = 100)\n"
                         "Initial upper bound: inf\nLower bound function: lb1_d\nBranching rule: fwd\n"
                         "=================================================\n")
 
