@@ -85,8 +85,8 @@ def test_op_model_matches_reference_formulas():
 
 
 def test_unsupported_sizes_are_refused_loudly():
-    ins = bb.Instance(inst=31)  # 50 jobs: the reference needs a rebuild with MAX_JOBS=50 (pfsp/README.md:52)
-    with pytest.raises(bb.BBError, match="50 jobs"):
+    ins = bb.Instance(inst=61)  # 100 jobs: beyond the 50-job classes this build covers (pfsp/README.md:52)
+    with pytest.raises(bb.BBError, match="100 jobs"):
         bb.Engine.pfsp(ins, 0)
     with pytest.raises(bb.BBError):
         bb.Engine.nqueens(21)

@@ -73,6 +73,7 @@ def test_oracle50_matches_reference_directly(inst):
 # ------------------------------------------------------------------ GPU
 
 @pytest.mark.gpu
+@pytest.mark.timeout(240, method="thread")
 @pytest.mark.parametrize("inst", [31, 41, 51])
 @pytest.mark.parametrize("lb", [0, 1, 2])
 def test_wide_one_iteration_children_match_oracle(inst, lb):
@@ -101,9 +102,12 @@ def test_wide_one_iteration_children_match_oracle(inst, lb):
 
 
 @pytest.mark.gpu
+@pytest.mark.timeout(240, method="thread")
 def test_wide_whole_searches_match_oracle():
     """whole trees: the 50-job instances the reference solves at the root (ta032, ta034: 3 nodes, counts printed by
-    the rebuilt pfsp_c, tests/golden/wide.json) and random 24..30-job instances walked by the checker"""
+    the rebuilt pfsp_c, tests/golden/wide.json), and searches of ta031 / ta041 / ta051 and of random 26..40-job
+    instances below an upper bound that no leaf can improve (best0 a little above the root's bound: the tree is then
+    the set of nodes with lb < best0, a constant of (instance, bound, best0) like the reference's trees at the optimum)"""
     from __graft_entry__ import load_package
     bb = load_package()
     L = orc.oracle(50)
@@ -111,17 +115,26 @@ def test_wide_whole_searches_match_oracle():
         res, per = bb.pfsp_search(bb.Instance(inst=r["inst"]), r["lb"], M=1 << 16)
         assert (res.tree, res.sol, res.best) == (r["tree"], r["sol"], r["makespan"]), r
     rng = np.random.default_rng(5)
-    for n, m in ((24, 5), (27, 10), (30, 7)):
+    cases = [(bb.Instance(inst=i), L.orc_pfsp_new(i)) for i in (31, 41, 51)]
+    for n, m in ((26, 5), (33, 10), (40, 7)):
         p = rng.integers(1, 100, size=(m, n)).astype(np.int32)
-        ins = bb.Instance(p_times=p)
-        h = L.orc_pfsp_from_ptimes(n, m, np.ascontiguousarray(p.reshape(-1)))
+        cases.append((bb.Instance(p_times=p), L.orc_pfsp_from_ptimes(n, m, np.ascontiguousarray(p.reshape(-1)))))
+    compared = 0
+    for ins, h in cases:
+        n = ins.n
+        root = np.arange(n, dtype=np.int32)
+        lbb = np.zeros(n, np.int32)
+        L.orc_lb1_children(h, root, -1, n, lbb)
+        base = int(lbb.min())
         st = orc.RunStats()
-        res, _ = bb.pfsp_search(ins, 2, best0=INT_MAX, M=1 << 16)   # -u 0: finds the optimum
-        opt = res.best
-        for lb in (2, 0, 1):
-            L.orc_pfsp_search(h, lb, opt, 3_000_000, C.byref(st))
-            if st.parents >= 3_000_000:
-                continue  # the checker's budget ran out: this bound's tree is too large for a CPU test
-            res, per = bb.pfsp_search(ins, lb, best0=opt, M=1 << 16)
-            assert (res.tree, res.sol, res.best) == (st.tree, st.sol, opt), (n, m, lb)
+        for lb in (0, 1, 2):
+            for delta in (3, 12, 30):
+                best0 = base + delta
+                L.orc_pfsp_search(h, lb, best0, 400_000, C.byref(st))
+                if st.parents >= 400_000 or st.best != best0:
+                    break  # the checker's budget ran out, or a leaf improved the bound: not a constant tree
+                res, per = bb.pfsp_search(ins, lb, best0=best0, M=1 << 14)
+                assert (res.tree, res.sol, res.best) == (st.tree, st.sol, best0), (n, ins.m, lb, delta)
+                compared += 1
         L.orc_pfsp_free(h)
+    assert compared >= 12
