@@ -28,8 +28,8 @@
  * stall samples of the LB2 variant and 36 % of the LB1_d variant sat on its return, another 11 % / 33 % on the load of
  * the incumbent, which shared the cursor's cache line). So a tile's pass 2 runs one tile LATE: the warp issues the
  * reservation for tile t, bounds tile t+1, and only then writes tile t's children - three tile buffers rotate
- * (pass 2 pending / being bounded / being prefetched with cp.async) and two survivor lists. The incumbent is loaded
- * one tile ahead as well and lives in a different cache line than the cursor (bb_ctrl).
+ * (pass 2 pending / being bounded / being prefetched with cp.async) and two survivor lists. The incumbent is read
+ * once per launch and lives in a different cache line than the cursor (bb_ctrl).
  * Results are bit-identical to the earlier kernels (same child set, same counters).
  */
 #ifndef BB_PFSP_TPP_CUH
@@ -255,7 +255,11 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   /* the tile whose children are still to be written (its cursor reservation is in flight) */
   int pend_nsurv = 0, pend_buf = 0, pend_sbuf = 0;
   unsigned pend_pos = 0;
-  int best_next = *reinterpret_cast<volatile int *>(&ctrl->best);
+  /* the incumbent is read ONCE per launch, before any asynchronous copy is in flight: the reference's kernels get
+   * `best` by value at launch too (PFSP_gpu_lib.cu:148). A per-tile load, even issued a tile ahead, ended up on the
+   * scoreboard slot of the tile prefetch and made the first compare of every tile wait for HBM (a fifth of the LB1_d
+   * kernel's stall samples). Leaves still lower ctrl->best at once; the next launch prunes with it. */
+  const int best = *reinterpret_cast<volatile int *>(&ctrl->best);
   fetch_tile(blockIdx.x * BB_WARPS_PER_CTA + warp, tile_buf);
   for (int tile = blockIdx.x * BB_WARPS_PER_CTA + warp; tile < ntiles; tile += tstride)
   {
@@ -266,8 +270,6 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     fetch_tile(tile + tstride, tile_buf + nbuf * (NPL * 32)); /* the third buffer: neither current nor pending */
     asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
-    const int best = best_next;
-    best_next = *reinterpret_cast<volatile int *>(&ctrl->best); /* used by the next tile: its latency is hidden */
     const int first = tile * TS;
     const int cnt = min(TS, nbatch - first);
     const bool mine = lane < cnt;
