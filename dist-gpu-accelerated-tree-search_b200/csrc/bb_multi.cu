@@ -640,6 +640,10 @@ extern "C" int bb_dist_search(bb_dist *d, int best0, int ws, bb_search_result *r
   if (mine)
     *mine = st;
   res->elapsed_s = now_s() - t0;
+  if (getenv("BB_TRACE_PHASES"))
+    fprintf(stderr, "[bb rank %d] call %.3f ms: entry barriers %.3f, warm-up %.3f, span %.3f, stats+final barrier %.3f\n",
+            rank, res->elapsed_s * 1e3, (s0 - t0) * 1e3, warm_s * 1e3, search_s * 1e3,
+            (now_s() - s0 - search_s) * 1e3);
   return rc;
 }
 

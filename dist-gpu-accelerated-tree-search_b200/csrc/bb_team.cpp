@@ -79,10 +79,27 @@ inline void st(int *p, int v) { __atomic_store_n(p, v, __ATOMIC_SEQ_CST); }
 inline long long ldll(const long long *p) { return __atomic_load_n(p, __ATOMIC_SEQ_CST); }
 inline void stll(long long *p, long long v) { __atomic_store_n(p, v, __ATOMIC_SEQ_CST); }
 
+inline double now_ms();
+
+/* short waits are spun (nanosleep rounds a 20-50 us request up to 70-120 us with the default timer slack, and a
+ * search on 8 GPUs lasts only tens of milliseconds); one worker per GPU leaves the host cores for it */
 inline void nap(unsigned us)
 {
-  struct timespec ts = {0, (long)us * 1000L};
-  nanosleep(&ts, nullptr);
+  if (us >= 200)
+  {
+    struct timespec ts = {0, (long)us * 1000L};
+    nanosleep(&ts, nullptr);
+    return;
+  }
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  do
+  {
+#if defined(__x86_64__) || defined(__i386__)
+    __builtin_ia32_pause();
+#endif
+    clock_gettime(CLOCK_MONOTONIC, &t1);
+  } while ((t1.tv_sec - t0.tv_sec) * 1000000L + (t1.tv_nsec - t0.tv_nsec) / 1000L < (long)us);
 }
 
 inline double now_ms()

@@ -8,7 +8,7 @@ if [ "${2:-}" = "tests" ]; then
 fi
 for w in pfsp:21:2 nq:17; do
   out=gpurun_out/r2/bench_n${N}_${w//:/_}
-  BB_TRACE_TEAM=${BB_TRACE_TEAM:-} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 \
+  BB_TRACE_PHASES=${BB_TRACE_PHASES:-} BB_TRACE_TEAM=${BB_TRACE_TEAM:-} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 \
     bench.py --gpus $N --steps 5 --warmup 3 --workload $w > $out.json 2> $out.err
   echo "== $w N=$N rc=$?"
   python - <<PY
