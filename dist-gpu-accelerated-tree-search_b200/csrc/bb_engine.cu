@@ -728,7 +728,11 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   const size_t sz_ord = ((size_t)((P > 0 ? P : 1) + 1) * 4 + 15) & ~(size_t)15;
   const size_t canon = sz_p8 + 2 * sz_vec + 3 * sz_slot + sz_pairs;
   /* + the learned-order copies of the four pair tables, order[], score[], hist[] (device-written) */
-  const size_t total = canon + 3 * sz_slot + sz_pairs + 3 * sz_ord;
+  /* + the lane-per-parent kernel's processing-time rows, [word][job] with four machines per word, ready to be copied
+   * into shared memory as they are (one TMA bulk copy per CTA) */
+  const size_t off_prow = canon + 3 * sz_slot + sz_pairs + 3 * sz_ord;
+  const size_t sz_prow = (size_t)((BB_MAX_MACHINES + 3) / 4) * BB_MAX_JOBS * 4;
+  const size_t total = off_prow + sz_prow;
   std::vector<unsigned char> h(total, 0);
   uint8_t *p8 = h.data();
   int *tails = (int *)(h.data() + sz_p8);
@@ -762,6 +766,15 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
       jb[l * BB_MAX_JOBS + q] = ins->lags[s * n + job] + ins->p_times[m2 * n + job];
     }
   }
+  {
+    const int mu = bbk::pfsp_mm(m) ? bbk::pfsp_mm(m) : BB_MAX_MACHINES;
+    uint32_t *prow = (uint32_t *)(h.data() + off_prow);
+    for (int q = 0; q < (mu + 3) / 4; q++)
+      for (int j = 0; j < BB_MAX_JOBS; j++)
+        for (int b = 0; b < 4; b++)
+          if (4 * q + b < m)
+            prow[q * BB_MAX_JOBS + j] |= (uint32_t)p8[(4 * q + b) * BB_MAX_JOBS + j] << (8 * b);
+  }
   BB_CUDA_TRY(cudaMalloc(&e->table_mem, total));
   BB_CUDA_TRY(cudaMemcpy(e->table_mem, h.data(), total, cudaMemcpyHostToDevice));
   e->table_bytes = total;
@@ -784,6 +797,7 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   e->T.order = (int *)(d + canon + 3 * sz_slot + sz_pairs);
   e->T.score = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + sz_ord);
   e->T.hist = (unsigned *)(d + canon + 3 * sz_slot + sz_pairs + 2 * sz_ord);
+  e->T.prow = (const uint32_t *)(d + off_prow);
   e->T.best_known = ins->best_known;
   e->T.one = 1u;
   for (int k = 0; k < BB_MAX_MACHINES; k++)

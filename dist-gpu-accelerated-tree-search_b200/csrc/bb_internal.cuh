@@ -106,6 +106,7 @@ struct bb_pfsp_dev
    * the unrolled machine loop reads it as a constant-bank operand */
   uint32_t tails2[BB_MAX_MACHINES];
   int best_known;
+  const uint32_t *prow; /* [ceil(mu/4)][BB_MAX_JOBS]: word q of job j = its times on machines 4q..4q+3 (bb_pfsp_tpp.cuh) */
   uint32_t one; /* 1 at run time: multiplier of the IMAD that does an add on the FMA pipe (bb_pfsp_tpp.cuh) */
 };
 

@@ -30,6 +30,11 @@
  * reservation for tile t, bounds tile t+1, and only then writes tile t's children - three tile buffers rotate
  * (pass 2 pending / being bounded / being prefetched with cp.async) and two survivor lists. The incumbent is read
  * once per launch and lives in a different cache line than the cursor (bb_ctrl).
+ * The processing-time rows are staged in shared memory with one TMA bulk copy per CTA (cp.async.bulk on an mbarrier:
+ * the table is contiguous and already in its shared-memory layout). The parent tiles stay on per-lane cp.async:
+ * one TMA bulk copy per record plane (512 contiguous bytes in the pool and in the tile) was measured too and is
+ * slower at a prefetch distance of one tile (ta022 / LB1_d 39.3 -> 41.8 ms, ta021 / LB2 425 -> 431 ms); a longer
+ * distance needs a fourth tile buffer that shared memory does not have at m = 20.
  * Results are bit-identical to the earlier kernels (same child set, same counters).
  */
 #ifndef BB_PFSP_TPP_CUH
@@ -42,7 +47,7 @@ namespace bbk
 
 struct tpp_smem_layout
 {
-  int off_prow, off_warp, warp_bytes, off_tile, off_surv, total;
+  int off_prow, off_mbar, off_warp, warp_bytes, off_tile, off_surv, total;
 };
 
 /* machines (compile-time class MM as in pfsp_mm; 0 = runtime m <= 20) -> shared-memory layout of pfsp_expand3 */
@@ -54,6 +59,8 @@ __host__ __device__ inline tpp_smem_layout tpp_layout(int m)
   int o = 0;
   L.off_prow = o; /* [pw][BB_MAX_JOBS] u32: word q of job j = times of j on machines 4q..4q+3, one byte each */
   o += (pw * BB_MAX_JOBS * 4 + 15) & ~15;
+  L.off_mbar = o; /* mbarrier of the TMA bulk copy that stages the rows */
+  o += 16;
   L.off_warp = o;
   int w = 0;
   L.off_tile = w; /* 3 x [plane][32] uint4: pass 2 pending, being bounded, being prefetched */
@@ -117,17 +124,32 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
   uint4 *tile_buf = reinterpret_cast<uint4 *>(wbase + L.off_tile);
 
-  for (int i = threadIdx.x; i < PW * BB_MAX_JOBS; i += BB_CTA_THREADS)
+  /* ---- stage the processing-time rows: ONE TMA bulk copy per CTA (cp.async.bulk, 1-D: the table is contiguous and
+   * already in its shared-memory layout), completion on an mbarrier ---- */
   {
-    const int q = i / BB_MAX_JOBS, j = i - q * BB_MAX_JOBS;
-    uint32_t v = 0;
-#pragma unroll
-    for (int b = 0; b < 4; b++)
-      if (4 * q + b < m)
-        v |= (uint32_t)T.p8[(4 * q + b) * BB_MAX_JOBS + j] << (8 * b);
-    prow[i] = v;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(smem + L.off_mbar);
+    constexpr unsigned bytes = PW * BB_MAX_JOBS * 4;
+    static_assert(bytes % 16 == 0, "bulk copies move multiples of 16 bytes");
+    if (threadIdx.x == 0)
+    {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar) : "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       (unsigned)__cvta_generic_to_shared(prow)),
+                   "l"(T.prow), "r"(bytes), "r"(mbar)
+                   : "memory");
+    }
+    __syncthreads(); /* the initialised barrier is visible to every thread before it waits */
+    unsigned done = 0;
+    for (int spin = 0; spin < (1 << 22) && !done; spin++) /* bounded: a failed copy raises the error flag, not a hang */
+      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}"
+                   : "=r"(done)
+                   : "r"(mbar)
+                   : "memory");
+    if (!done && threadIdx.x == 0)
+      atomicExch(&ctrl->error, 1);
   }
-  __syncthreads();
 
   const uint4 *__restrict__ splanes = pool.planes[src];
   uint4 *__restrict__ dplanes = pool.planes[dst];
