@@ -42,6 +42,8 @@
 
 #include "bb_pfsp_kernels.cuh"
 
+#include <type_traits>
+
 namespace bbk
 {
 
@@ -331,14 +333,17 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
       cnt6[2] += cnt;
       cnt6[3] += allkids;
     }
-    const bool leaf = (kids == 1); /* the only child completes the schedule */
+    const bool leaf_lane = (kids == 1); /* the only child completes the schedule */
 
     /* ---- pass 1: bound this parent's children two at a time, remember the survivors by position ---- */
     uint32_t keepmask = 0u;
-    for (int it = 0; it < iters; it++)
-    {
+    /* iterations in which EVERY lane has two children to bound - nearly all, the lanes of a warp being at the same
+     * depth - run a copy of the body without per-lane activity and leaf tests */
+    const int full_iters = __reduce_min_sync(0xffffffffu, kids >> 1);
+    auto pair_iter = [&](const int it, auto fast_tag) {
+      constexpr bool FAST = decltype(fast_tag)::value;
       const int k0 = depth + 2 * it;
-      const bool act0 = k0 < n, act1 = k0 + 1 < n;
+      const bool act0 = FAST || k0 < n, act1 = FAST || k0 + 1 < n;
       const int kk0 = act0 ? k0 : 0, kk1 = act1 ? k0 + 1 : kk0;
       const int job0 = act0 ? tile_b[(kk0 >> 4) * 512 + lane * 16 + (kk0 & 15)] : 0;
       const int job1 = act1 ? tile_b[(kk1 >> 4) * 512 + lane * 16 + (kk1 & 15)] : job0;
@@ -377,6 +382,7 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         }
       }
       const int lbA = (int)(lb2 & 0xffffu), lbB = (int)(lb2 >> 16);
+      const bool leaf = !FAST && leaf_lane;
       if (act0 && leaf)
       {
         /* PFSP_lib.h:64-71: a leaf counts as a solution and may improve the incumbent */
@@ -428,6 +434,13 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         }
       }
       keepmask |= (keepA ? (1u << kk0) : 0u) | (keepB ? (1u << kk1) : 0u);
+    };
+    {
+      int it = 0;
+      for (; it < full_iters; it++)
+        pair_iter(it, std::true_type{});
+      for (; it < iters; it++)
+        pair_iter(it, std::false_type{});
     }
 
     /* ---- survivors of the tile: (lane, position) list in shared memory ---- */
