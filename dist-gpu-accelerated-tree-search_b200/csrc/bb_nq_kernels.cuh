@@ -602,7 +602,7 @@ nq_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
  *            child), every child written at round base + tile base + index. No atomics, no waiting.
  * Plane 1 is read twice per parent, the second time from L2 (a launch's plane 1 is 64 MB at M = 4 M).
  */
-#define NQ4_ROUND 4096
+#define NQ4_ROUND 2048
 
 __global__ void __launch_bounds__(BB_CTA_THREADS, 4)
 nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
@@ -620,6 +620,7 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
   __shared__ unsigned round_base;
   __shared__ uint4 tile_all[BB_WARPS_PER_CTA][2][2 * 32];
   __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS];
+  __shared__ __align__(16) unsigned char stage_all[BB_WARPS_PER_CTA][32 * 48]; /* per lane: one child being built */
   uint16_t *surv_s = surv_all[warp];
 
   const uint4 *__restrict__ splanes = pool.planes[src];
@@ -779,29 +780,23 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
             }
           }
           k += (__ffs(z) - 1) >> 3;
-          /* swap board[depth] <-> board[k] (nqueens_c.c:107-111): byte k takes the old board[depth], byte depth r */
-          uint32_t bd = 0;
-#pragma unroll
-          for (int wi = 0; wi < 5; wi++)
-            if (wi == (depth >> 2))
-              bd = (w[wi] >> (8 * (depth & 3))) & 0xffu;
-          const uint32_t x = bd ^ (uint32_t)r;
-#pragma unroll
-          for (int wi = 0; wi < 5; wi++)
-          {
-            uint32_t patch = 0;
-            if (wi == (depth >> 2))
-              patch ^= x << (8 * (depth & 3));
-            if (wi == (k >> 2))
-              patch ^= x << (8 * (k & 3));
-            w[wi] ^= patch;
-          }
+          /* swap board[depth] <-> board[k] (nqueens_c.c:107-111): byte k takes the old board[depth], byte depth r.
+           * The child record is assembled in a per-lane staging slot of shared memory and the two bytes are patched
+           * with byte stores: patching them in registers needs the words chosen by depth and k, i.e. a select chain
+           * over five words for each (a third of this pass's instructions before). */
           const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
           const uint32_t up2 = ((q1.z | bit) << 1) & full;
           const uint32_t down2 = (q1.w | bit) >> 1;
+          unsigned char *st = stage_all[warp] + lane * 48; /* bytes 0..19 = board, 20.. = the three mask words */
+          *reinterpret_cast<uint4 *>(st) = q0;
+          *reinterpret_cast<uint4 *>(st + 16) = make_uint4(q1.x, used2, up2, down2);
+          const unsigned char bd = st[depth];
+          st[depth] = (unsigned char)r;
+          st[k] = bd;
+          const uint4 c0 = *reinterpret_cast<const uint4 *>(st), c1 = *reinterpret_cast<const uint4 *>(st + 16);
           const size_t slot = (size_t)rbase + tile_base[t] + i;
-          dplanes[slot] = make_uint4(w[0], w[1], w[2], w[3]);
-          dplanes[(size_t)cap + slot] = make_uint4(w[4], used2, up2, down2);
+          dplanes[slot] = c0;
+          dplanes[(size_t)cap + slot] = c1;
         }
       __syncwarp();
     }
