@@ -639,38 +639,50 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
     const int rcnt = min(NQ4_ROUND, hi - r0);
     const int rtiles = (rcnt + 31) >> 5;
     /* ---- phase 1: free masks and child counts of the round ---- */
-    for (int i = threadIdx.x; i < rtiles * 32; i += BB_CTA_THREADS)
     {
-      uint32_t fr = 0u;
-      int kids = 0, cands = 0;
-      bool leaf = false;
-      if (i < rcnt)
+      /* all of a thread's loads of the round are issued before the first is used (the loop used to wait for each
+       * one in turn: 29 % of the kernel's stall samples); the counters are kept per thread - finish_iteration sums
+       * them over the CTA - so the only warp reduction left is the tile's child total */
+      constexpr int P1 = NQ4_ROUND / BB_CTA_THREADS;
+      uint4 q[P1];
+#pragma unroll
+      for (int j = 0; j < P1; j++)
       {
-        const uint4 q1 = __ldg(splanes + (size_t)cap + base + r0 + i);
-        const int depth = (int)(q1.y >> 24);
-        uint32_t used = q1.y & 0x00ffffffu;
-        leaf = (depth + 1 == N);
-        cands = N - depth;
+        const int i = threadIdx.x + j * BB_CTA_THREADS;
+        q[j] = make_uint4(0u, 0xff000000u, 0u, 0u); /* depth 255: no parent here */
+        if (i < rcnt)
+          q[j] = __ldg(splanes + (size_t)cap + base + r0 + i);
+      }
+      int akids = 0, asol = 0, acand = 0;
+#pragma unroll
+      for (int j = 0; j < P1; j++)
+      {
+        const int i = threadIdx.x + j * BB_CTA_THREADS;
+        const int depth = (int)(q[j].y >> 24);
+        const bool valid = depth != 255;
+        uint32_t used = q[j].y & 0x00ffffffu;
+        const bool leaf = (depth + 1 == N);
+        uint32_t fr = 0u;
         for (int g = 0; g < G; g++)
         {
           asm volatile("" : "+r"(used)); /* keep the G repetitions as real work, as the reference's -g intends */
-          fr = ~(used | q1.z | q1.w) & full;
+          fr = ~(used | q[j].z | q[j].w) & full;
         }
-        kids = __popc(fr);
+        if (!valid)
+          fr = 0u;
+        const int kids = __popc(fr);
+        const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
+        free_s[i] = leaf ? 0u : fr;
+        akids += kids; /* exploredTree counts every safe placement, leaves included */
+        asol += leaf ? kids : 0;
+        acand += valid ? N - depth : 0;
+        const int tot = __reduce_add_sync(0xffffffffu, wkids);
+        if (lane == 0)
+          tile_base[i >> 5] = tot;
       }
-      const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
-      free_s[i] = leaf ? 0u : fr;
-      const int tot = __reduce_add_sync(0xffffffffu, wkids);
-      const int allkids = __reduce_add_sync(0xffffffffu, kids);
-      const int allsol = __reduce_add_sync(0xffffffffu, leaf ? kids : 0);
-      const int allcand = __reduce_add_sync(0xffffffffu, cands);
-      if (lane == 0)
-      {
-        tile_base[i >> 5] = tot;
-        cnt6[0] += allkids; /* exploredTree counts every safe placement, leaves included */
-        cnt6[1] += allsol;
-        cnt6[3] += allcand;
-      }
+      cnt6[0] += akids;
+      cnt6[1] += asol;
+      cnt6[3] += acand;
     }
     if (threadIdx.x == 0)
       cnt6[2] += rcnt;
