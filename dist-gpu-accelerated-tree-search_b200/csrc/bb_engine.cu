@@ -969,7 +969,12 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
     int rc = alloc_common(e, cfg, 2, 0);
     if (rc)
       return rc;
-    rc = setup_launch(e, c_nq4 ? (const void *)bbk::nq_expand4 : (const void *)bbk::nq_expand3, 0);
+    const bool c_nq5 = getenv("BB_NQ_CTA_ROUNDS") == nullptr; /* debugging aid: nq_expand4 reserves per CTA round */
+    rc = setup_launch(e,
+                      !c_nq4  ? (const void *)bbk::nq_expand3
+                      : c_nq5 ? (const void *)bbk::nq_expand5
+                              : (const void *)bbk::nq_expand4,
+                      0);
     if (rc)
       return rc;
     return build_graph(e);

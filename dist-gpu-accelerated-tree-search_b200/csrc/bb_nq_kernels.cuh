@@ -818,5 +818,193 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
   finish_iteration(ctrl, cnt6, src, base, cap);
 }
 
+/*
+ * Fifth-generation N-Queens kernel: nq_expand4 without its CTA barriers. ncu on nq_expand4 showed the warps of a CTA
+ * waiting for each other three times per round (phase 1 -> scan by warp 0 -> phase 2 -> next round) and for the
+ * round's loads all at the same moment. Here every WARP owns a slice of the batch and works in rounds of
+ * NQ5_TILES tiles on its own: 32 x NQ5_TILES parents read (all loads in flight together), free masks to the warp's
+ * shared memory, the round's child total by NQ5_TILES warp reductions, ONE atomicAdd on the cursor per round
+ * (16 384 per 4 M-parent launch, an eighth of what made per-tile reservation the limiter), then the round's tiles
+ * exactly as nq_expand4's phase 2 with a running offset instead of a tile table. No __syncthreads until the
+ * counters are summed; a warp waiting for its loads or its reservation is covered by the 31 others on the SM.
+ */
+#define NQ5_TILES 8
+
+__global__ void __launch_bounds__(BB_CTA_THREADS, 4)
+nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+{
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int cap = pool.capacity;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t full = (N >= 32) ? 0xffffffffu : ((1u << N) - 1u);
+
+  __shared__ uint32_t free_all[BB_WARPS_PER_CTA][NQ5_TILES * 32]; /* written and read by the same lane */
+  __shared__ uint4 tile_all[BB_WARPS_PER_CTA][2][2 * 32];
+  __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS];
+  __shared__ __align__(16) unsigned char stage_all[BB_WARPS_PER_CTA][32 * 48];
+  uint32_t *free_s = free_all[warp];
+  uint16_t *surv_s = surv_all[warp];
+
+  const uint4 *__restrict__ splanes = pool.planes[src];
+  uint4 *__restrict__ dplanes = pool.planes[dst];
+
+  unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
+  int akids = 0, asol = 0, acand = 0, apar = 0;
+
+  /* this warp's slice: a multiple of 32 parents */
+  const int nw = (int)gridDim.x * BB_WARPS_PER_CTA, gw = (int)blockIdx.x * BB_WARPS_PER_CTA + warp;
+  const int per = (((nbatch + nw - 1) / nw) + 31) & ~31;
+  const long long lo_ll = (long long)gw * per;
+  const int lo = lo_ll < nbatch ? (int)lo_ll : nbatch;
+  const int hi = min(nbatch, lo + per);
+
+  for (int r0 = lo; r0 < hi; r0 += NQ5_TILES * 32)
+  {
+    const int rcnt = min(NQ5_TILES * 32, hi - r0);
+    const int rtiles = (rcnt + 31) >> 5;
+    auto fetch_tile = [&](int t, uint4 *dstbuf) {
+      if (t < rtiles)
+      {
+        const int first = t * 32;
+        if (lane < min(32, rcnt - first))
+        {
+          const size_t node = (size_t)base + r0 + first + lane;
+#pragma unroll
+          for (int q = 0; q < 2; q++)
+          {
+            const unsigned sa = (unsigned)__cvta_generic_to_shared(dstbuf + q * 32 + lane);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(splanes + (size_t)q * cap + node)
+                         : "memory");
+          }
+        }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    fetch_tile(0, tile_all[warp][0]);
+    /* ---- the round's free masks and child total ---- */
+    int total = 0;
+    {
+      uint4 q[NQ5_TILES];
+#pragma unroll
+      for (int j = 0; j < NQ5_TILES; j++)
+      {
+        const int i = j * 32 + lane;
+        q[j] = make_uint4(0u, 0xff000000u, 0u, 0u); /* depth 255: no parent here */
+        if (i < rcnt)
+          q[j] = __ldg(splanes + (size_t)cap + base + r0 + i);
+      }
+#pragma unroll
+      for (int j = 0; j < NQ5_TILES; j++)
+      {
+        const int depth = (int)(q[j].y >> 24);
+        const bool valid = depth != 255;
+        uint32_t used = q[j].y & 0x00ffffffu;
+        const bool leaf = (depth + 1 == N);
+        uint32_t fr = 0u;
+        for (int g = 0; g < G; g++)
+        {
+          asm volatile("" : "+r"(used)); /* keep the G repetitions as real work, as the reference's -g intends */
+          fr = ~(used | q[j].z | q[j].w) & full;
+        }
+        if (!valid)
+          fr = 0u;
+        const int kids = __popc(fr);
+        const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
+        free_s[j * 32 + lane] = leaf ? 0u : fr;
+        akids += kids; /* exploredTree counts every safe placement, leaves included */
+        asol += leaf ? kids : 0;
+        acand += valid ? N - depth : 0;
+        apar += valid ? 1 : 0;
+        total += __reduce_add_sync(0xffffffffu, wkids);
+      }
+    }
+    unsigned rbase = 0;
+    if (total)
+    {
+      if (lane == 0)
+      {
+        rbase = atomicAdd(&ctrl->tail, (unsigned)total);
+        if (rbase + (unsigned)total > (unsigned)cap)
+        {
+          atomicExch(&ctrl->error, 1);
+          rbase = 0xffffffffu; /* nothing of this round is written */
+        }
+      }
+      rbase = __shfl_sync(0xffffffffu, rbase, 0);
+    }
+
+    /* ---- the round's tiles, one lane per child, no atomics ---- */
+    int buf = 0, off = 0;
+    for (int t = 0; t < rtiles; t++)
+    {
+      const uint4 *tile_s = tile_all[warp][buf];
+      fetch_tile(t + 1, tile_all[warp][buf ^ 1]);
+      buf ^= 1;
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+      __syncwarp();
+      uint32_t f = free_s[t * 32 + lane];
+      const int nk = __popc(f);
+      const int incl = warp_incl_scan(nk, lane);
+      const int nsurv = __shfl_sync(0xffffffffu, incl, 31);
+      int at = incl - nk;
+      while (f)
+      {
+        const int r = __ffs(f) - 1;
+        f &= f - 1u;
+        surv_s[at++] = (uint16_t)((lane << 8) | r);
+      }
+      __syncwarp();
+      if (rbase != 0xffffffffu)
+        for (int i = lane; i < nsurv; i += 32)
+        {
+          const int e = surv_s[i];
+          const int p = e >> 8, r = e & 0xff;
+          const uint4 q0 = tile_s[p], q1 = tile_s[32 + p];
+          uint32_t w[5] = {q0.x, q0.y, q0.z, q0.w, q1.x};
+          const int depth = (int)(q1.y >> 24);
+          const uint32_t bit = 1u << r;
+          const uint32_t rrrr = (uint32_t)r * 0x01010101u;
+          uint32_t z = nq_has_byte(w[4], rrrr);
+          int k = 16;
+#pragma unroll
+          for (int wi = 3; wi >= 0; wi--)
+          {
+            const uint32_t zz = nq_has_byte(w[wi], rrrr);
+            if (zz)
+            {
+              z = zz;
+              k = 4 * wi;
+            }
+          }
+          k += (__ffs(z) - 1) >> 3;
+          const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
+          const uint32_t up2 = ((q1.z | bit) << 1) & full;
+          const uint32_t down2 = (q1.w | bit) >> 1;
+          unsigned char *st = stage_all[warp] + lane * 48;
+          *reinterpret_cast<uint4 *>(st) = q0;
+          *reinterpret_cast<uint4 *>(st + 16) = make_uint4(q1.x, used2, up2, down2);
+          const unsigned char bd = st[depth];
+          st[depth] = (unsigned char)r;
+          st[k] = bd;
+          const uint4 c0 = *reinterpret_cast<const uint4 *>(st), c1 = *reinterpret_cast<const uint4 *>(st + 16);
+          const size_t slot = (size_t)rbase + off + i;
+          dplanes[slot] = c0;
+          dplanes[(size_t)cap + slot] = c1;
+        }
+      off += nsurv;
+      __syncwarp();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  }
+  cnt6[0] = (unsigned long long)akids;
+  cnt6[1] = (unsigned long long)asol;
+  cnt6[2] = (unsigned long long)apar;
+  cnt6[3] = (unsigned long long)acand;
+  finish_iteration(ctrl, cnt6, src, base, cap);
+}
+
 } // namespace bbk
 #endif
