@@ -853,6 +853,13 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 
   unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0};
   int akids = 0, asol = 0, acand = 0, apar = 0;
+  uint32_t vmask[5]; /* high bit of every board byte below N */
+#pragma unroll
+  for (int wi = 0; wi < 5; wi++)
+  {
+    const int nb = min(4, max(0, N - 4 * wi));
+    vmask[wi] = nb == 4 ? 0x80808080u : (0x80808080u & ((1u << (8 * nb)) - 1u));
+  }
 
   /* this warp's slice: a multiple of 32 parents */
   const int nw = (int)gridDim.x * BB_WARPS_PER_CTA, gw = (int)blockIdx.x * BB_WARPS_PER_CTA + warp;
@@ -913,12 +920,15 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
           fr = 0u;
         const int kids = __popc(fr);
         const int wkids = leaf ? 0 : kids; /* depth-N children are counted, not stored (nqueens_c.c:103-105) */
-        free_s[j * 32 + lane] = leaf ? 0u : fr;
         akids += kids; /* exploredTree counts every safe placement, leaves included */
         asol += leaf ? kids : 0;
         acand += valid ? N - depth : 0;
         apar += valid ? 1 : 0;
-        total += __reduce_add_sync(0xffffffffu, wkids);
+        /* the lane's first index in the tile's child list is found here, where NQ5_TILES independent scans overlap,
+         * and travels with the mask: rows in bits 0..19, index (< 640) above */
+        const int incl = warp_incl_scan(wkids, lane);
+        free_s[j * 32 + lane] = (leaf ? 0u : fr) | ((uint32_t)(incl - wkids) << 20);
+        total += __shfl_sync(0xffffffffu, incl, 31);
       }
     }
     unsigned rbase = 0;
@@ -945,11 +955,10 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
       buf ^= 1;
       asm volatile("cp.async.wait_group 1;" ::: "memory");
       __syncwarp();
-      uint32_t f = free_s[t * 32 + lane];
-      const int nk = __popc(f);
-      const int incl = warp_incl_scan(nk, lane);
-      const int nsurv = __shfl_sync(0xffffffffu, incl, 31);
-      int at = incl - nk;
+      const uint32_t packed = free_s[t * 32 + lane];
+      uint32_t f = packed & 0xfffffu;
+      int at = (int)(packed >> 20);
+      const int nsurv = __shfl_sync(0xffffffffu, at + __popc(f), 31);
       while (f)
       {
         const int r = __ffs(f) - 1;
@@ -966,20 +975,20 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
           uint32_t w[5] = {q0.x, q0.y, q0.z, q0.w, q1.x};
           const int depth = (int)(q1.y >> 24);
           const uint32_t bit = 1u << r;
+          /* where row r sits in the board: the board holds every row once in bytes 0..N-1 (the padding bytes are
+           * masked off), so exactly one word has a matching byte; the flag of byte j of word i is moved to bit
+           * 8j + 7 - i and the lowest set bit is the match (the zero-byte test may also flag bytes ABOVE a true
+           * match in the same word, never below) */
           const uint32_t rrrr = (uint32_t)r * 0x01010101u;
-          uint32_t z = nq_has_byte(w[4], rrrr);
-          int k = 16;
+          uint32_t mm = 0u;
 #pragma unroll
-          for (int wi = 3; wi >= 0; wi--)
+          for (int wi = 0; wi < 5; wi++)
           {
-            const uint32_t zz = nq_has_byte(w[wi], rrrr);
-            if (zz)
-            {
-              z = zz;
-              k = 4 * wi;
-            }
+            const uint32_t x = w[wi] ^ rrrr;
+            mm |= ((x - 0x01010101u) & ~x & vmask[wi]) >> wi;
           }
-          k += (__ffs(z) - 1) >> 3;
+          const int hb = __ffs(mm) - 1;
+          const int k = 4 * (7 - (hb & 7)) + (hb >> 3);
           const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
           const uint32_t up2 = ((q1.z | bit) << 1) & full;
           const uint32_t down2 = (q1.w | bit) >> 1;
