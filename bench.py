@@ -536,7 +536,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.M <= 0:
-        args.M = 1 << 21 if w[0] == "pfsp" else 1 << 22
+        # measured optimum per workload on one B200 (scripts/gpu_sweep_m.sh, gpu_sweep_m2.sh): the fill and drain of
+        # a launch are amortised over more parents up to here; beyond, the launches get slower per parent
+        args.M = (1 << 23 if w[2] == 2 else 1 << 22) if w[0] == "pfsp" else 1 << 23
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":

@@ -821,8 +821,8 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 /*
  * Fifth-generation N-Queens kernel: nq_expand4 without its CTA barriers. ncu on nq_expand4 showed the warps of a CTA
  * waiting for each other three times per round (phase 1 -> scan by warp 0 -> phase 2 -> next round) and for the
- * round's loads all at the same moment. Here every WARP owns a slice of the batch and works in rounds of
- * NQ5_TILES tiles on its own: 32 x NQ5_TILES parents read (all loads in flight together), free masks to the warp's
+ * round's loads all at the same moment. Here every WARP works on its own, in rounds of up to NQ5_TILES tiles
+ * taken from a counter (ctrl->next_round): 32 x NQ5_TILES parents read (all loads in flight together), free masks to the warp's
  * shared memory, the round's child total by NQ5_TILES warp reductions, ONE atomicAdd on the cursor per round
  * (16 384 per 4 M-parent launch, an eighth of what made per-tile reservation the limiter), then the round's tiles
  * exactly as nq_expand4's phase 2 with a running offset instead of a tile table. No __syncthreads until the
@@ -833,6 +833,7 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 __global__ void __launch_bounds__(BB_CTA_THREADS, 4)
 nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
 {
+  pdl_wait_then_release(); /* the plan and the pool are the previous iteration's output */
   const int nbatch = ctrl->n;
   if (nbatch == 0)
     return;
@@ -861,16 +862,25 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
     vmask[wi] = nb == 4 ? 0x80808080u : (0x80808080u & ((1u << (8 * nb)) - 1u));
   }
 
-  /* this warp's slice: a multiple of 32 parents */
-  const int nw = (int)gridDim.x * BB_WARPS_PER_CTA, gw = (int)blockIdx.x * BB_WARPS_PER_CTA + warp;
-  const int per = (((nbatch + nw - 1) / nw) + 31) & ~31;
-  const long long lo_ll = (long long)gw * per;
-  const int lo = lo_ll < nbatch ? (int)lo_ll : nbatch;
-  const int hi = min(nbatch, lo + per);
+  /* rounds are handed out through a counter, and get smaller towards the end of the batch (each warp asks for
+   * what it saw left / the number of warps, at most NQ5_TILES tiles, at least one): with equal static slices the
+   * launch ended with most SMs waiting for the slowest warps to finish whole rounds */
+  const int nw = (int)gridDim.x * BB_WARPS_PER_CTA;
+  const int T = (nbatch + 31) >> 5;
+  int seen = 0;
 
-  for (int r0 = lo; r0 < hi; r0 += NQ5_TILES * 32)
+  for (;;)
   {
-    const int rcnt = min(NQ5_TILES * 32, hi - r0);
+    const int want = min(NQ5_TILES, max(1, (T - seen) / nw));
+    int t0 = 0;
+    if (lane == 0)
+      t0 = (int)atomicAdd(&ctrl->next_round, (unsigned)want);
+    t0 = __shfl_sync(0xffffffffu, t0, 0);
+    if (t0 >= T)
+      break;
+    seen = t0 + want;
+    const int r0 = t0 * 32;
+    const int rcnt = min(want * 32, nbatch - r0);
     const int rtiles = (rcnt + 31) >> 5;
     auto fetch_tile = [&](int t, uint4 *dstbuf) {
       if (t < rtiles)
@@ -906,6 +916,8 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 #pragma unroll
       for (int j = 0; j < NQ5_TILES; j++)
       {
+        if (j * 32 >= rcnt) /* warp-uniform */
+          break;
         const int depth = (int)(q[j].y >> 24);
         const bool valid = depth != 255;
         uint32_t used = q[j].y & 0x00ffffffu;

@@ -172,6 +172,16 @@ __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
   c->tile = tile < 1 ? 1 : (tile > BB_TILE_MAX ? BB_TILE_MAX : tile);
   c->ticket = 0;
   c->next_tile = 0;
+  c->next_round = 0;
+}
+
+/* programmatic dependent launch (bb_engine.cu launches the chained iterations with
+ * cudaLaunchAttributeProgrammaticStreamSerialization): block until the previous grid has completed and its writes are
+ * visible, then allow the next grid of the chain to be scheduled */
+__device__ __forceinline__ void pdl_wait_then_release()
+{
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 /* counters accumulated per thread, reduced per warp -> CTA -> one global atomic each; then the last CTA to

@@ -104,9 +104,6 @@ __global__ void __launch_bounds__(BB_CTA_THREADS, ((LB == 3 || MM == 20 || MM ==
 pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T, const int prefilter)
 {
   static_assert(LB == 0 || LB == 1 || LB == 3, "lane-per-parent kernel: LB1_d, LB1, LB2 through the subset table");
-  const int nbatch = ctrl->n;
-  if (nbatch == 0)
-    return;
   constexpr int MU = MM ? MM : BB_MAX_MACHINES;
   constexpr int MP = MM ? ((MM + 1) & ~1) : BB_MAX_MACHINES;
   constexpr int NPL = (6 + MP + 3) / 4;
@@ -116,7 +113,6 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   const int n = T.n;
   const int P = T.P;
   const int cap = pool.capacity;
-  const int src = ctrl->src, dst = 1 - src, base = ctrl->base, TS = ctrl->tile;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t one = T.one;
 
@@ -152,6 +148,16 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
     if (!done && threadIdx.x == 0)
       atomicExch(&ctrl->error, 1);
   }
+
+  /* Everything above touches only this launch's shared memory and a table that never changes, so under
+   * programmatic dependent launch it runs while the previous iteration is still finishing. The plan and the pool
+   * are the previous iteration's output: wait for it, then let the next launch start its own prologue as soon as
+   * SM resources free up. (Both are no-ops for a launch without the attribute.) */
+  pdl_wait_then_release();
+  const int nbatch = ctrl->n;
+  if (nbatch == 0)
+    return;
+  const int src = ctrl->src, dst = 1 - src, base = ctrl->base, TS = ctrl->tile;
 
   const uint4 *__restrict__ splanes = pool.planes[src];
   uint4 *__restrict__ dplanes = pool.planes[dst];
