@@ -130,7 +130,7 @@ def runs():
         {"N": 15, "tree": 171129071, "sol": 2279184},
         {"N": 16, "tree": 1141190302, "sol": 14772512},
         {"N": 17, "tree": 8017021931, "sol": 95815104},
-        {"N": 18, "tree": 59365844490, "sol": 666090624, "predicted": True},
+        {"N": 18, "tree": 59365844490, "sol": 666090624},  # printed by nqueens_c.out -N 18 -g 1 (ref_gpu_runs.json, 9067 s)
     ]
     return out
 
