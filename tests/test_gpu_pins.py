@@ -19,12 +19,12 @@ def test_whole_tree_equals_what_the_reference_printed(key):
     parts = key.split(":")
     if parts[0] == "pfsp":
         inst, lb = int(parts[1]), int(parts[2])
-        res, per = bb.pfsp_search(bb.Instance(inst=inst), lb, M=1 << 21)
+        res, per = bb.pfsp_search(bb.Instance(inst=inst), lb, M=1 << 22)
         assert (res.tree, res.sol, res.best) == (r["tree"], r["sol"], r["makespan"]), (key, r["command"])
         assert per[0].parents == res.tree + 1
     else:
         N = int(parts[1])
-        res, per = bb.nq_search(N, 1, M=1 << 22)
+        res, per = bb.nq_search(N, 1, M=1 << 23)
         assert (res.tree, res.sol) == (r["tree"], r["sol"]), (key, r["command"])
         assert per[0].parents == res.tree - res.sol + 1
 
