@@ -164,6 +164,9 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
   const uint32_t fullmask = (n >= 32) ? 0xffffffffu : ((1u << n) - 1u);
 
   unsigned long long cnt6[6] = {0, 0, 0, 0, 0, 0}; /* tree, sol, parents, evals, lb2_evals, lb2_pairs */
+  const unsigned char *g16_bytes = reinterpret_cast<const unsigned char *>(T.g16);
+  const unsigned grow_bytes = (unsigned)T.grow * 2u;
+  unsigned nlb2 = 0u; /* this lane's table evaluations of the launch (a 64-bit counter in the pair loop cost 7 % of its instructions) */
 
   const int ntiles = (nbatch + TS - 1) / TS;
   const int tstride = gridDim.x * BB_WARPS_PER_CTA;
@@ -408,8 +411,9 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
         {
           constexpr int NV = (MU - 1 + 7) / 8; /* uint4 loads per row */
           const uint32_t UA = U0 & ~(1u << job0), UB = U0 & ~(1u << job1);
-          const uint4 *rowA = reinterpret_cast<const uint4 *>(T.g16 + (size_t)UA * T.grow);
-          const uint4 *rowB = reinterpret_cast<const uint4 *>(T.g16 + (size_t)UB * T.grow);
+          /* base + set x row bytes: one IMAD.WIDE each on the FMA pipe */
+          const uint4 *rowA = reinterpret_cast<const uint4 *>(g16_bytes + (size_t)UA * grow_bytes);
+          const uint4 *rowB = reinterpret_cast<const uint4 *>(g16_bytes + (size_t)UB * grow_bytes);
           uint4 ga[NV], gb[NV];
 #pragma unroll
           for (int q = 0; q < NV; q++)
@@ -434,9 +438,10 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
           }
           keepA = candA && ((int)(v2 & 0xffffu) < best);
           keepB = candB && ((int)(v2 >> 16) < best);
-          const int ne = (candA ? 1 : 0) + (candB ? 1 : 0);
-          cnt6[4] += ne;
-          cnt6[5] += (unsigned long long)ne * P;
+          if (candA)
+            nlb2++;
+          if (candB)
+            nlb2++;
         }
       }
       keepmask |= (keepA ? (1u << kk0) : 0u) | (keepB ? (1u << kk1) : 0u);
@@ -488,6 +493,8 @@ pfsp_expand3(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_dev T
                    pend_pos);
   asm volatile("cp.async.wait_group 0;" ::: "memory");
 
+  cnt6[4] = nlb2; /* children bounded through the table; every one stands for the P machine pairs of lb2_bound */
+  cnt6[5] = (unsigned long long)nlb2 * P;
   finish_iteration(ctrl, cnt6, src, base, cap);
 }
 
