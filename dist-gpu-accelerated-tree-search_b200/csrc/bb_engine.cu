@@ -95,7 +95,7 @@ struct bb_engine
   void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
-  /* PFSP, 21..50 jobs (bb_pfsp_wide.cuh): wider record, its own tables */
+  /* PFSP, 21..100 jobs (bb_pfsp_wide.cuh): wider record, its own tables; 0, or the job-capacity class 50 / 100 */
   int wide;
   bb_pfsp_wide_dev TW;
   void *wide_mem;
@@ -312,18 +312,19 @@ __global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int sta
     nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
 }
 
-/* 21..50 jobs: the reference's Node built with MAX_JOBS 50 (int16 depth, limit1, prmu[50]) <-> the wide record */
+/* 21..100 jobs: the reference's Node built with MAX_JOBS NJ (int16 depth, limit1, prmu[NJ]) <-> the wide record */
+template <int NJ>
 __global__ void k_seed_pfsp_wide(const int16_t *__restrict__ nodes, int count, bb_pool pool, bb_pfsp_wide_dev T, int at)
 {
+  using G = wide_geom<NJ>;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
-  const int16_t *nd = nodes + (size_t)i * (2 + BB_WIDE_JOBS);
+  const int16_t *nd = nodes + (size_t)i * (2 + NJ);
   const int depth = nd[0];
-  uint32_t w[BB_WIDE_PLANES * 4];
-  for (int q = 0; q < BB_WIDE_PLANES * 4; q++)
+  uint32_t w[G::NPL * 4];
+  for (int q = 0; q < G::NPL * 4; q++)
     w[q] = 0;
-  unsigned long long mask = 0;
   int front[BB_MAX_MACHINES], remain[BB_MAX_MACHINES];
   for (int k = 0; k < T.m; k++)
     front[k] = remain[k] = 0;
@@ -333,35 +334,36 @@ __global__ void k_seed_pfsp_wide(const int16_t *__restrict__ nodes, int count, b
     w[j >> 2] |= (uint32_t)job << (8 * (j & 3));
     if (j < depth)
     {
-      mask |= 1ull << job;
+      w[G::W_MASK + (job >> 5)] |= 1u << (job & 31);
       front[0] += T.p8[job];
       for (int k = 1; k < T.m; k++)
-        front[k] = max(front[k - 1], front[k]) + T.p8[k * BB_WIDE_STRIDE + job];
+        front[k] = max(front[k - 1], front[k]) + T.p8[k * G::STRIDE + job];
     }
     else
       for (int k = 0; k < T.m; k++)
-        remain[k] += T.p8[k * BB_WIDE_STRIDE + job];
+        remain[k] += T.p8[k * G::STRIDE + job];
   }
-  w[BB_WIDE_W_DEPTH] = (uint32_t)depth;
-  w[BB_WIDE_W_MASK] = (uint32_t)mask;
-  w[BB_WIDE_W_MASK + 1] = (uint32_t)(mask >> 32);
+  w[G::W_DEPTH] = (uint32_t)depth;
   uint16_t *h = reinterpret_cast<uint16_t *>(w);
   for (int k = 0; k < T.m; k++)
   {
-    h[2 * BB_WIDE_W_FRONT + k] = (uint16_t)front[k];
-    h[2 * BB_WIDE_W_REMAIN + k] = (uint16_t)remain[k];
+    h[2 * G::W_FRONT + k] = (uint16_t)front[k];
+    h[2 * G::W_REMAIN + k] = (uint16_t)remain[k];
   }
-  for (int q = 0; q < BB_WIDE_PLANES; q++)
+  for (int q = 0; q < G::NPL; q++)
     pool.planes[0][(size_t)q * pool.capacity + at + i] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
 }
 
+template <int NJ>
 __global__ void k_export_pfsp_wide(int16_t *__restrict__ nodes, bb_pool pool, int stack, int from, int count, int out_at)
 {
+  using G = wide_geom<NJ>;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count)
     return;
-  uint32_t w[16];
-  for (int q = 0; q < 4; q++)
+  constexpr int HP = (G::W_DEPTH + 4) / 4; /* planes holding prmu[] and the depth word */
+  uint32_t w[HP * 4];
+  for (int q = 0; q < HP; q++)
   {
     const uint4 v = pool.planes[stack][(size_t)q * pool.capacity + from + i];
     w[4 * q] = v.x;
@@ -369,11 +371,11 @@ __global__ void k_export_pfsp_wide(int16_t *__restrict__ nodes, bb_pool pool, in
     w[4 * q + 2] = v.z;
     w[4 * q + 3] = v.w;
   }
-  int16_t *nd = nodes + (size_t)(out_at + i) * (2 + BB_WIDE_JOBS);
-  const int depth = w[BB_WIDE_W_DEPTH] & 0xff;
+  int16_t *nd = nodes + (size_t)(out_at + i) * (2 + NJ);
+  const int depth = w[G::W_DEPTH] & 0xff;
   nd[0] = (int16_t)depth;
   nd[1] = (int16_t)(depth - 1);
-  for (int j = 0; j < BB_WIDE_JOBS; j++)
+  for (int j = 0; j < NJ; j++)
     nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
 }
 
@@ -820,21 +822,22 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   return BB_OK;
 }
 
-/* 21..50 jobs: tables of bb_pfsp_wide_dev in one allocation, the wide kernel of the requested bound */
+/* 21..100 jobs: tables of bb_pfsp_wide_dev in one allocation, the wide kernel of the requested bound and class */
 static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
 {
   e->kind = KIND_PFSP;
-  e->wide = 1;
+  e->wide = wide_class(ins->nb_jobs); /* job-capacity class of the record and of the host's Node: 50 or 100 */
   e->lb = lb;
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
   e->prefilter = cfg ? (cfg->lb2_prefilter != 0) : 1;
-  int rc = alloc_common(e, cfg, BB_WIDE_PLANES, 0);
+  const int NJ = e->wide, WS = wide_stride(NJ);
+  int rc = alloc_common(e, cfg, wide_planes(NJ), 0);
   if (rc)
     return rc;
   const int n = e->n, m = e->m, P = ins->nb_machine_pairs > 0 ? ins->nb_machine_pairs : 0, P1 = P > 0 ? P : 1;
-  const size_t sz_p8 = (size_t)m * BB_WIDE_STRIDE, sz_tails = ((size_t)m * 4 + 15) & ~(size_t)15;
-  const size_t sz_jjob = (size_t)P1 * BB_WIDE_STRIDE, sz_int = (size_t)P1 * BB_WIDE_STRIDE * 4, sz_pairs = (size_t)P1 * 8;
+  const size_t sz_p8 = (size_t)m * WS, sz_tails = ((size_t)m * 4 + 15) & ~(size_t)15;
+  const size_t sz_jjob = (size_t)P1 * WS, sz_int = (size_t)P1 * WS * 4, sz_pairs = (size_t)P1 * 8;
   const size_t o_tails = (sz_p8 + 15) & ~(size_t)15, o_jjob = o_tails + sz_tails, o_ja = (o_jjob + sz_jjob + 15) & ~(size_t)15;
   const size_t o_jb = o_ja + sz_int, o_pairs = o_jb + sz_int, total = o_pairs + sz_pairs;
   std::vector<unsigned char> h(total, 0);
@@ -845,7 +848,7 @@ static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, c
       const int v = ins->p_times[k * n + j];
       if (v < 0 || v > 255)
         return bb_fail(BB_ERR_ARG, "processing time %d out of the supported 0..255 range", v);
-      h[(size_t)k * BB_WIDE_STRIDE + j] = (unsigned char)v;
+      h[(size_t)k * WS + j] = (unsigned char)v;
     }
     ((int *)(h.data() + o_tails))[k] = ins->min_tails[k];
   }
@@ -858,9 +861,9 @@ static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, c
     for (int q = 0; q < n; q++)
     {
       const int job = ins->johnson_schedules[sidx * n + q];
-      h[o_jjob + (size_t)l * BB_WIDE_STRIDE + q] = (unsigned char)job;
-      ((int *)(h.data() + o_ja))[(size_t)l * BB_WIDE_STRIDE + q] = ins->p_times[m2 * n + job] - ins->p_times[m1 * n + job];
-      ((int *)(h.data() + o_jb))[(size_t)l * BB_WIDE_STRIDE + q] = ins->lags[sidx * n + job] + ins->p_times[m2 * n + job];
+      h[o_jjob + (size_t)l * WS + q] = (unsigned char)job;
+      ((int *)(h.data() + o_ja))[(size_t)l * WS + q] = ins->p_times[m2 * n + job] - ins->p_times[m1 * n + job];
+      ((int *)(h.data() + o_jb))[(size_t)l * WS + q] = ins->lags[sidx * n + job] + ins->p_times[m2 * n + job];
     }
   }
   BB_CUDA_TRY(cudaMalloc(&e->wide_mem, total));
@@ -879,10 +882,13 @@ static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, c
   e->T.n = n; /* the generic code paths read n / m from here */
   e->T.m = m;
   e->T.P = P;
-  const void *k = lb == 0   ? (const void *)bbk::pfsp_expand_wide<0>
-                  : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1>
-                            : (const void *)bbk::pfsp_expand_wide<2>;
-  rc = setup_launch(e, k, bbk::wide_layout(m).total);
+  const void *k = NJ == 50 ? (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 50>
+                              : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 50>
+                                        : (const void *)bbk::pfsp_expand_wide<2, 50>)
+                           : (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 100>
+                              : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 100>
+                                        : (const void *)bbk::pfsp_expand_wide<2, 100>);
+  rc = setup_launch(e, k, bbk::wide_layout(m, NJ).total);
   if (rc)
     return rc;
   return build_graph(e);
@@ -1023,11 +1029,11 @@ extern "C" bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb,
     bb_fail(BB_ERR_ARG, "bb_pfsp_engine_create: bad instance or lower bound %d", lb);
     return nullptr;
   }
-  if (ins->nb_jobs > BB_WIDE_JOBS || ins->nb_machines > BB_MAX_MACHINES)
+  if (ins->nb_jobs > BB_MAX_JOBS_WIDE || ins->nb_machines > BB_MAX_MACHINES)
   {
     /* the reference needs a rebuild with a larger MAX_JOBS for these (pfsp/README.md:52); refuse loudly */
     bb_fail(BB_ERR_ARG, "instance has %d jobs x %d machines; this build supports at most %d x %d", ins->nb_jobs,
-            ins->nb_machines, BB_WIDE_JOBS, BB_MAX_MACHINES);
+            ins->nb_machines, BB_MAX_JOBS_WIDE, BB_MAX_MACHINES);
     return nullptr;
   }
   bb_engine *e = (bb_engine *)calloc(1, sizeof(bb_engine));
@@ -1180,12 +1186,12 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
   const int at = e->ctrl_h->size[0];
   if ((long long)at + count > e->pool.capacity)
     return bb_fail(BB_ERR_OVERFLOW, "pool capacity %d exceeded while seeding %d nodes", e->pool.capacity, count);
-  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? e->wide : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
   if (e->kind == KIND_PFSP)
   {
     /* nodes the engine cannot represent are rejected here rather than silently mis-handled */
     const int16_t *nd = (const int16_t *)host_nodes;
-    const size_t st16 = 2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS);
+    const size_t st16 = 2 + (e->wide ? e->wide : BB_MAX_JOBS);
     for (int i = 0; i < count; i++)
       if (nd[(size_t)i * st16] < 0 || nd[(size_t)i * st16] >= e->n)
         return bb_fail(BB_ERR_ARG, "node %d has depth %d outside 0..%d", i, nd[(size_t)i * st16], e->n - 1);
@@ -1206,8 +1212,10 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
   if (err == cudaSuccess)
   {
     const int blocks = (count + 127) / 128;
-    if (e->kind == KIND_PFSP && e->wide)
-      k_seed_pfsp_wide<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
+    if (e->kind == KIND_PFSP && e->wide == 50)
+      k_seed_pfsp_wide<50><<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
+    else if (e->kind == KIND_PFSP && e->wide)
+      k_seed_pfsp_wide<100><<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
     else if (e->kind == KIND_PFSP)
       k_seed_pfsp<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->T, at, e->T.mp,
                                                  e->pool.nplanes);
@@ -1232,7 +1240,7 @@ extern "C" int bb_engine_push_root(bb_engine *e)
     return bb_fail(BB_ERR_ARG, "null engine");
   if (e->kind == KIND_PFSP)
   {
-    int16_t nd[2 + BB_WIDE_JOBS]; /* a 20-job engine reads the first 2 + 20 entries */
+    int16_t nd[2 + BB_MAX_JOBS_WIDE]; /* an engine reads the first 2 + 20 / 50 / 100 entries */
     memset(nd, 0, sizeof(nd));
     nd[0] = 0;
     nd[1] = -1;
@@ -1261,7 +1269,7 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     return bb_fail(BB_ERR_ARG, "export buffer holds %lld nodes, pool has %lld", max_count, total);
   if (total == 0)
     return 0;
-  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? BB_WIDE_JOBS : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
+  const size_t rec = e->kind == KIND_PFSP ? sizeof(int16_t) * (2 + (e->wide ? e->wide : BB_MAX_JOBS)) : (1 + BB_MAX_QUEENS);
   void *stage = nullptr;
   rc = pool_alloc(e, &stage, rec * total);
   if (rc)
@@ -1273,8 +1281,10 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     if (!cnt)
       continue;
     const int blocks = (cnt + 127) / 128;
-    if (e->kind == KIND_PFSP && e->wide)
-      k_export_pfsp_wide<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
+    if (e->kind == KIND_PFSP && e->wide == 50)
+      k_export_pfsp_wide<50><<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
+    else if (e->kind == KIND_PFSP && e->wide)
+      k_export_pfsp_wide<100><<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else if (e->kind == KIND_PFSP)
       k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else if (e->nq_gen == 3)
@@ -1555,8 +1565,8 @@ int bb_engine_zero_counters(bb_engine *e)
  * the root to the same SET of nodes; it keeps the nodes whose placed prefix hashes to its id and drops the others, in
  * place, stack by stack (one CTA: the warm-up pool is a few thousand nodes). A content hash needs no communication
  * and does not depend on the order in which the device appended the nodes.
- * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4), 2: N-Queens plane + tail words, 3: PFSP record
- * of the 50-job classes. */
+ * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4/5), 2: N-Queens plane + tail words, 3 / 4: PFSP
+ * record of the 50- / 100-job classes. */
 __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, int mode, int nq_dbyte, int D, int me,
                                                    int total_warps)
 {
@@ -1570,7 +1580,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
     for (int c0 = from; c0 < to; c0 += blockDim.x)
     {
       const int i = c0 + threadIdx.x;
-      uint4 pl[BB_WIDE_PLANES];
+      uint4 pl[wide_geom<100>::NPL]; /* the widest record */
       uint32_t tw[2] = {0u, 0u};
       bool keep = false;
       if (i < to)
@@ -1579,34 +1589,27 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
           pl[q] = pool.planes[s][(size_t)q * pool.capacity + i];
         for (int t = 0; t < pool.tail_words; t++)
           tw[t] = pool.tailw[s][(size_t)i * pool.tail_words + t];
-        uint32_t w[13] = {pl[0].x, pl[0].y, pl[0].z, pl[0].w, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        /* the permutation starts at byte 0 of the record in every layout; only mode 2 continues in the tail words */
+        const uint32_t *pw = reinterpret_cast<const uint32_t *>(pl);
+        auto byte_at = [&](int b) -> unsigned {
+          const uint32_t word = (mode == 2 && b >= 16) ? tw[(b - 16) >> 2] : pw[b >> 2];
+          return (word >> (8 * (b & 3))) & 0xffu;
+        };
         int depth;
         if (mode == 3)
-        { /* wide PFSP record: prmu in words 0..12, depth in word 13 */
-          const uint4 a = pl[1], b = pl[2], c4 = pl[3];
-          w[4] = a.x, w[5] = a.y, w[6] = a.z, w[7] = a.w, w[8] = b.x, w[9] = b.y, w[10] = b.z, w[11] = b.w, w[12] = c4.x;
-          depth = (int)(c4.y & 0xffu);
-        }
+          depth = (int)(pw[wide_geom<50>::W_DEPTH] & 0xffu);
+        else if (mode == 4)
+          depth = (int)(pw[wide_geom<100>::W_DEPTH] & 0xffu);
         else if (mode == 0)
-        {
-          w[4] = pl[1].x;
           depth = (int)(pl[1].y & 0xffu);
-        }
         else if (mode == 1)
-        {
-          w[4] = pl[1].x;
           depth = (int)(pl[1].y >> 24);
-        }
         else
-        {
-          w[4] = tw[0];
-          w[5] = tw[1];
-          depth = (int)((w[nq_dbyte >> 2] >> (8 * (nq_dbyte & 3))) & 0xffu);
-        }
+          depth = (int)byte_at(nq_dbyte);
         unsigned h = 2166136261u; /* FNV-1a over the placed prefix */
         for (int b = 0; b < depth; b++)
         {
-          h ^= (w[b >> 2] >> (8 * (b & 3))) & 0xffu;
+          h ^= byte_at(b);
           h *= 16777619u;
         }
         h ^= h >> 15;
@@ -1650,7 +1653,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
 int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters)
 {
   ENGINE_SET_DEVICE(e);
-  int mode = e->wide ? 3 : 0, dbyte = 0;
+  int mode = e->wide == 50 ? 3 : e->wide ? 4 : 0, dbyte = 0;
   if (e->kind == KIND_NQ)
   {
     mode = e->nq_gen == 3 ? 1 : 2;

@@ -1,9 +1,11 @@
 /*
- * bb_pfsp_wide.cuh - fused bound -> prune -> branch -> compact for the 50-job Taillard classes (ta031-ta060).
+ * bb_pfsp_wide.cuh - fused bound -> prune -> branch -> compact for the 50- and 100-job Taillard classes
+ * (ta031-ta060, ta061-ta090).
  *
  * The reference handles instances above 20 jobs by editing MAX_JOBS in pfsp/lib/macro.h:10 and rebuilding
  * (pfsp/README.md:52); its kernels and host code are otherwise the same. Here the engine switches to this kernel and
- * a wider record when an instance has 21..50 jobs:
+ * a wider record when an instance has 21..100 jobs (two job-capacity classes, wide_geom<50> and wide_geom<100>: the
+ * reference's MAX_JOBS; the layout below is the 50-job one, the 100-job record has 25 prmu words, 4 mask words, 13 planes):
  *     words  0..12   prmu[50] as uint8 (first `depth` entries = scheduled prefix)
  *     word   13      depth
  *     words 14..15   scheduled-set bitmask (64 bits)
@@ -25,23 +27,34 @@
 
 #include "bb_pfsp_kernels.cuh"
 
-#define BB_WIDE_JOBS 50
-#define BB_WIDE_STRIDE 64 /* jobs / Johnson slots per row in the wide tables */
-#define BB_WIDE_PLANES 9
-#define BB_WIDE_W_DEPTH 13
-#define BB_WIDE_W_MASK 14
-#define BB_WIDE_W_FRONT 16
-#define BB_WIDE_W_REMAIN 26
+/* record geometry of a job-capacity class NJ (50: ta031-ta060, 100: ta061-ta090), in 32-bit words */
+template <int NJ>
+struct wide_geom
+{
+  static_assert(NJ == 50 || NJ == 100, "job-capacity classes of the wide kernel");
+  static constexpr int JOBS = NJ;
+  static constexpr int STRIDE = NJ == 50 ? 64 : 128; /* jobs / Johnson slots per row in the wide tables */
+  static constexpr int PRW = (NJ + 3) / 4;           /* words of prmu[]: 13 / 25 */
+  static constexpr int W_DEPTH = PRW;                /* 13 / 25 */
+  static constexpr int W_MASK = PRW + 1;             /* 14 / 26 */
+  static constexpr int MW = (NJ + 31) / 32;          /* words of the scheduled-set bitmask: 2 / 4 */
+  static constexpr int W_FRONT = W_MASK + MW;        /* 16 / 30 */
+  static constexpr int W_REMAIN = W_FRONT + BB_MAX_MACHINES / 2; /* 26 / 40 */
+  static constexpr int NPL = (W_REMAIN + BB_MAX_MACHINES / 2 + 3) / 4; /* planes of 16 bytes: 9 / 13 */
+};
+__host__ __device__ inline int wide_class(int n) { return n <= 50 ? 50 : 100; }
+__host__ __device__ inline int wide_stride(int nj) { return nj == 50 ? 64 : 128; }
+__host__ __device__ inline int wide_planes(int nj) { return nj == 50 ? wide_geom<50>::NPL : wide_geom<100>::NPL; }
 
 /* instance tables of a wide engine (device global memory) */
 struct bb_pfsp_wide_dev
 {
   int n, m, P;
-  const uint8_t *p8;   /* [m][BB_WIDE_STRIDE] processing times */
+  const uint8_t *p8;   /* [m][STRIDE] processing times (STRIDE = wide_geom<NJ>::STRIDE) */
   const int *tails;    /* [m] min_tails */
-  const uint8_t *jjob; /* [P][BB_WIDE_STRIDE] job in Johnson order of the pair (0xff past n) */
-  const int *ja;       /* [P][BB_WIDE_STRIDE] p[m2][job] - p[m1][job] */
-  const int *jb;       /* [P][BB_WIDE_STRIDE] lag + p[m2][job] */
+  const uint8_t *jjob; /* [P][STRIDE] job in Johnson order of the pair (0xff past n) */
+  const int *ja;       /* [P][STRIDE] p[m2][job] - p[m1][job] */
+  const int *jb;       /* [P][STRIDE] lag + p[m2][job] */
   const int2 *pairs;   /* (m1, m2) in the reference's evaluation order */
 };
 
@@ -53,22 +66,22 @@ struct wide_smem_layout
   int off_p8, off_tails, off_warp, warp_bytes, off_tile, off_offs, off_surv, off_fc, off_fr, total;
 };
 
-__host__ __device__ inline wide_smem_layout wide_layout(int m)
+__host__ __device__ inline wide_smem_layout wide_layout(int m, int nj)
 {
   wide_smem_layout L;
   int o = 0;
   L.off_p8 = o;
-  o += m * BB_WIDE_STRIDE;
+  o += m * wide_stride(nj);
   L.off_tails = o;
   o += ((m * 4) + 15) & ~15;
   L.off_warp = o;
   int w = 0;
   L.off_tile = w;
-  w += BB_WIDE_PLANES * BB_TILE_MAX * 16;
+  w += wide_planes(nj) * BB_TILE_MAX * 16;
   L.off_offs = w;
   w += 36 * 4;
-  L.off_surv = w; /* (parent << 8) | position, at most 32 x 50 */
-  w += BB_TILE_MAX * BB_WIDE_JOBS * 2;
+  L.off_surv = w; /* (parent << 8) | position, at most 32 x NJ */
+  w += BB_TILE_MAX * nj * 2;
   L.off_fc = w; /* [20][32] child front (LB2) */
   w += BB_MAX_MACHINES * 32 * 2;
   L.off_fr = w; /* [20][32] child front + remain (LB2) */
@@ -78,14 +91,17 @@ __host__ __device__ inline wide_smem_layout wide_layout(int m)
   return L;
 }
 
-template <int LB>
-__global__ void __launch_bounds__(BB_CTA_THREADS, 2)
+template <int LB, int NJ>
+__global__ void __launch_bounds__(BB_CTA_THREADS, NJ == 50 ? 2 : 1)
 pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_wide_dev T, const int prefilter)
 {
   const int nbatch = ctrl->n;
   if (nbatch == 0)
     return;
-  constexpr int NPL = BB_WIDE_PLANES;
+  using G = wide_geom<NJ>;
+  constexpr int NPL = G::NPL;
+  constexpr int BB_WIDE_STRIDE = G::STRIDE, BB_WIDE_W_DEPTH = G::W_DEPTH, BB_WIDE_W_MASK = G::W_MASK,
+                BB_WIDE_W_FRONT = G::W_FRONT, BB_WIDE_W_REMAIN = G::W_REMAIN;
   constexpr int MU = BB_MAX_MACHINES;
   const int m = T.m, n = T.n, P = T.P;
   const int cap = pool.capacity;
@@ -93,7 +109,7 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
   extern __shared__ __align__(16) unsigned char smem[];
-  const wide_smem_layout L = wide_layout(m);
+  const wide_smem_layout L = wide_layout(m, NJ);
   uint8_t *p8 = smem + L.off_p8;
   int *tails = reinterpret_cast<int *>(smem + L.off_tails);
   unsigned char *wbase = smem + L.off_warp + warp * L.warp_bytes;
@@ -163,8 +179,10 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
       const int depth = (int)(rdw(BB_WIDE_W_DEPTH) & 0xffu);
       const int k = act ? depth + (c - offs_s[p]) : depth;
       const int job = rec[(k >> 4) * 512 + (k & 15)];
-      const unsigned long long smask = (unsigned long long)rdw(BB_WIDE_W_MASK) |
-                                       ((unsigned long long)rdw(BB_WIDE_W_MASK + 1) << 32);
+      uint32_t unsched[G::MW]; /* jobs not scheduled in the CHILD: the parent's set plus this job, complemented */
+#pragma unroll
+      for (int wq = 0; wq < G::MW; wq++)
+        unsched[wq] = ~(rdw(BB_WIDE_W_MASK + wq) | (wq == (job >> 5) ? (1u << (job & 31)) : 0u));
 
       int fc[MU], rc[MU];
       int lb;
@@ -217,7 +235,6 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
         keep = cand;
         if (__ballot_sync(0xffffffffu, cand))
         {
-          const unsigned long long unsched = ~(smask | (1ull << job));
 #pragma unroll
           for (int i = 0; i < MU; i++)
             if (i < m)
@@ -241,7 +258,12 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
               for (int q = 0; q < n; q++)
               {
                 const int jq = __ldg(jj + q);
-                if ((unsched >> jq) & 1ull)
+                uint32_t uw = unsched[0];
+#pragma unroll
+                for (int wq = 1; wq < G::MW; wq++)
+                  if ((jq >> 5) == wq)
+                    uw = unsched[wq];
+                if ((uw >> (jq & 31)) & 1u)
                   D = add_max(D, __ldg(va + q), __ldg(vb + q));
               }
               const int val = (int)fr_s[ab.x * 32 + lane] + max(D + tails[ab.y], tails[ab.x]);
@@ -306,7 +328,7 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
           /* prmu: swap positions depth and k (PFSP_lib.h:80-82) */
           const uint32_t x = (uint32_t)(job ^ jobd);
 #pragma unroll
-          for (int wi = 0; wi < 13; wi++)
+          for (int wi = 0; wi < G::PRW; wi++)
           {
             uint32_t patch = 0;
             if (wi == (depth >> 2))
@@ -316,10 +338,10 @@ pfsp_expand_wide(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const bb_pfsp_w
             w[wi] ^= patch;
           }
           w[BB_WIDE_W_DEPTH] = (uint32_t)(depth + 1);
-          if (job < 32)
-            w[BB_WIDE_W_MASK] |= 1u << job;
-          else
-            w[BB_WIDE_W_MASK + 1] |= 1u << (job - 32);
+#pragma unroll
+          for (int wq = 0; wq < G::MW; wq++)
+            if (wq == (job >> 5))
+              w[BB_WIDE_W_MASK + wq] |= 1u << (job & 31);
           /* child front / remain (the same recurrence as in pass 1) */
           int t = 0;
 #pragma unroll

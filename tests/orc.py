@@ -40,7 +40,7 @@ _oracle = {}
 
 
 def oracle(max_jobs=20):
-    """the CPU checker; max_jobs = 50 loads the same code built with 50-job node records (liboracle50.so)"""
+    """the CPU checker; max_jobs = 50 / 100 loads the same code built with 50- / 100-job node records (liboracle<NJ>.so)"""
     if max_jobs in _oracle:
         return _oracle[max_jobs]
     path = os.path.join(ORACLE_DIR, "liboracle.so" if max_jobs == 20 else f"liboracle{max_jobs}.so")
@@ -84,12 +84,16 @@ _ref_pfsp = {}
 _ref_nq = None
 
 
+def have_ref_wide(max_jobs=50):
+    return os.path.exists(os.path.join(REF_DIR, f"libref_pfsp{max_jobs}.so"))
+
+
 def have_ref50():
-    return os.path.exists(os.path.join(REF_DIR, "libref_pfsp50.so"))
+    return have_ref_wide(50)
 
 
 def ref_pfsp(max_jobs=20):
-    """the compiled reference; max_jobs = 50 is the build with MAX_JOBS edited to 50 (make -C oracle ref50)"""
+    """the compiled reference; max_jobs = 50 / 100 is the build with MAX_JOBS edited (make -C oracle ref50 ref100)"""
     if max_jobs not in _ref_pfsp:
         L = C.CDLL(os.path.join(REF_DIR, "libref_pfsp.so" if max_jobs == 20 else f"libref_pfsp{max_jobs}.so"))
         L.ref_pfsp_open.restype = C.c_void_p

@@ -1,9 +1,9 @@
-"""The 50-job Taillard classes (ta031-ta060). The reference handles them by editing MAX_JOBS in pfsp/lib/macro.h:10
-and rebuilding (pfsp/README.md:52); the checker is the same restatement built with 50-job node records
-(oracle/liboracle50.so), pinned here against that rebuilt reference (oracle/_ref/libref_pfsp50.so, make -C oracle
-ref50) where it is present, and against tests/golden/wide.json (generated from it by tests/golden/make_golden_wide.py)
-everywhere. The GPU tests compare the engine's wide kernel with the checker through the C ABI: the child SET of one
-iteration for all three bounds, and whole searches."""
+"""The 50- and 100-job Taillard classes (ta031-ta090). The reference handles them by editing MAX_JOBS in
+pfsp/lib/macro.h:10 and rebuilding (pfsp/README.md:52); the checker is the same restatement built with 50- / 100-job
+node records (oracle/liboracle50.so, liboracle100.so), pinned here against that rebuilt reference
+(oracle/_ref/libref_pfsp<NJ>.so, make -C oracle ref50 ref100) where it is present, and against tests/golden/wide.json
+(generated from it by tests/golden/make_golden_wide.py) everywhere. The GPU tests compare the engine's wide kernel with
+the checker through the C ABI: the child SET of one iteration for all three bounds, and whole searches."""
 import ctypes as C
 
 import numpy as np
@@ -12,8 +12,12 @@ import pytest
 import orc
 from conftest import load_golden
 
-W = 2 + 50
 INT_MAX = 2**31 - 1
+
+
+def klass(inst):
+    """job-capacity class of a Taillard instance: MAX_JOBS of the reference build that handles it"""
+    return 50 if inst <= 60 else 100
 
 
 def chunk_bounds(L, h, n, lb, parents, best):
@@ -23,32 +27,33 @@ def chunk_bounds(L, h, n, lb, parents, best):
     return bounds[:nb]
 
 
-def golden_nodes(g):
-    return np.array(g["parents"], dtype=np.int16).reshape(-1, W)
+def golden_nodes(g, inst):
+    return np.array(g["parents"], dtype=np.int16).reshape(-1, 2 + klass(inst))
 
 
-@pytest.mark.parametrize("inst", [31, 41, 51])
-def test_oracle50_matches_reference_golden(inst):
-    """tables and chunk-level bounds of the 50-job checker against what the rebuilt reference produced"""
+@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81])
+def test_wide_oracle_matches_reference_golden(inst):
+    """tables and chunk-level bounds of the 50- / 100-job checker against what the rebuilt reference produced"""
     g = load_golden("wide")[str(inst)]
-    L = orc.oracle(50)
+    L = orc.oracle(klass(inst))
     h = L.orc_pfsp_new(inst)
     n, m = L.orc_taillard_jobs(inst), L.orc_taillard_machines(inst)
     t = orc.Tables(n, m, m * (m - 1) // 2)
     L.orc_pfsp_tables(h, *t.arrays())
     assert {k: "%016x" % orc.fnv(a) for k, a in zip(("p", "heads", "tails", "lags", "johnson"), t.arrays())} == g["fnv"]
     assert L.orc_taillard_best_ub(inst) == g["best"]
-    parents = golden_nodes(g)
+    parents = golden_nodes(g, inst)
     for lb in (0, 1, 2):
         got = chunk_bounds(L, h, n, lb, parents, g["best"])
         assert got.tolist() == g["bounds"][str(lb)], (inst, lb)
     L.orc_pfsp_free(h)
 
 
-@pytest.mark.skipif(not orc.have_ref50(), reason="oracle/_ref/libref_pfsp50.so not built (make -C oracle ref50)")
-@pytest.mark.parametrize("inst", [31, 45, 52])
-def test_oracle50_matches_reference_directly(inst):
-    L, R = orc.oracle(50), orc.ref_pfsp(50)
+@pytest.mark.parametrize("inst", [31, 45, 52, 62, 77, 84])
+def test_wide_oracle_matches_reference_directly(inst):
+    if not orc.have_ref_wide(klass(inst)):
+        pytest.skip("oracle/_ref/libref_pfsp%d.so not built (make -C oracle ref%d)" % (klass(inst), klass(inst)))
+    L, R = orc.oracle(klass(inst)), orc.ref_pfsp(klass(inst))
     h, r = L.orc_pfsp_new(inst), R.ref_pfsp_open(inst)
     n = L.orc_taillard_jobs(inst)
     best = L.orc_taillard_best_ub(inst)
@@ -74,19 +79,20 @@ def test_oracle50_matches_reference_directly(inst):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(240, method="thread")
-@pytest.mark.parametrize("inst", [31, 41, 51])
+@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81])
 @pytest.mark.parametrize("lb", [0, 1, 2])
 def test_wide_one_iteration_children_match_oracle(inst, lb):
     from __graft_entry__ import load_package
     bb = load_package()
-    L = orc.oracle(50)
+    L = orc.oracle(klass(inst))
+    W = 2 + klass(inst)
     ins = bb.Instance(inst=inst)
     n = ins.n
     h = L.orc_pfsp_new(inst)
     rng = np.random.default_rng(1000 * inst + lb)
     eng = bb.Engine.pfsp(ins, lb, M=100000)
     for best in (ins.best_known, ins.best_known + 400):
-        parents = orc.random_pfsp_nodes(rng, n, 3000, 0, n - 2, width=W)
+        parents = orc.random_pfsp_nodes(rng, n, 3000 if n <= 50 else 1200, 0, n - 2, width=W)
         parents[0, :2] = (0, -1)
         parents[0, 2:2 + n] = np.arange(n)
         eng.reset(best)
@@ -103,20 +109,24 @@ def test_wide_one_iteration_children_match_oracle(inst, lb):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(240, method="thread")
-def test_wide_whole_searches_match_oracle():
-    """whole trees: the 50-job instances the reference solves at the root (ta032, ta034: 3 nodes, counts printed by
-    the rebuilt pfsp_c, tests/golden/wide.json), and searches of ta031 / ta041 / ta051 and of random 26..40-job
-    instances below an upper bound that no leaf can improve (best0 a little above the root's bound: the tree is then
-    the set of nodes with lb < best0, a constant of (instance, bound, best0) like the reference's trees at the optimum)"""
+@pytest.mark.parametrize("nj", [50, 100])
+def test_wide_whole_searches_match_oracle(nj):
+    """whole trees: the instances the reference solves at the root (ta032, ta034, ta061, ta063, ta065, ta066, ta069:
+    counts printed by the rebuilt pfsp_c, tests/golden/wide.json), and searches of ta031 / ta041 / ta051 (ta061 / ta071
+    / ta081) and of random 26..40-job (60..90-job) instances below an upper bound that no leaf can improve (best0 a
+    little above the root's bound: the tree is then the set of nodes with lb < best0, a constant of (instance, bound,
+    best0) like the reference's trees at the optimum)"""
     from __graft_entry__ import load_package
     bb = load_package()
-    L = orc.oracle(50)
+    L = orc.oracle(nj)
     for r in load_golden("wide")["runs"]:
+        if klass(r["inst"]) != nj:
+            continue
         res, per = bb.pfsp_search(bb.Instance(inst=r["inst"]), r["lb"], M=1 << 16)
         assert (res.tree, res.sol, res.best) == (r["tree"], r["sol"], r["makespan"]), r
-    rng = np.random.default_rng(5)
-    cases = [(bb.Instance(inst=i), L.orc_pfsp_new(i)) for i in (31, 41, 51)]
-    for n, m in ((26, 5), (33, 10), (40, 7)):
+    rng = np.random.default_rng(5 + nj)
+    cases = [(bb.Instance(inst=i), L.orc_pfsp_new(i)) for i in ((31, 41, 51) if nj == 50 else (61, 71, 81))]
+    for n, m in (((26, 5), (33, 10), (40, 7)) if nj == 50 else ((60, 5), (75, 10), (90, 7))):
         p = rng.integers(1, 100, size=(m, n)).astype(np.int32)
         cases.append((bb.Instance(p_times=p), L.orc_pfsp_from_ptimes(n, m, np.ascontiguousarray(p.reshape(-1)))))
     compared = 0
@@ -130,11 +140,64 @@ def test_wide_whole_searches_match_oracle():
         for lb in (0, 1, 2):
             for delta in (3, 12, 30):
                 best0 = base + delta
-                L.orc_pfsp_search(h, lb, best0, 400_000, C.byref(st))
-                if st.parents >= 400_000 or st.best != best0:
+                L.orc_pfsp_search(h, lb, best0, 400_000 if nj == 50 else 150_000, C.byref(st))
+                if st.parents >= (400_000 if nj == 50 else 150_000) or st.best != best0:
                     break  # the checker's budget ran out, or a leaf improved the bound: not a constant tree
                 res, per = bb.pfsp_search(ins, lb, best0=best0, M=1 << 14)
                 assert (res.tree, res.sol, res.best) == (st.tree, st.sol, best0), (n, ins.m, lb, delta)
                 compared += 1
         L.orc_pfsp_free(h)
-    assert compared >= 12
+    assert compared >= (12 if nj == 50 else 6)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(240, method="thread")
+@pytest.mark.parametrize("inst", [41, 51, 71, 81])
+@pytest.mark.parametrize("lb", [0, 1, 2])
+def test_wide_subtrees_below_deep_seeds_match_oracle(inst, lb):
+    """searches to exhaustion that are not trivial at 50 / 100 jobs: 40 random nodes with six jobs left are seeded and
+    everything below them is explored. (a) Without an upper bound and with a batch that takes a whole level (all
+    seeds have the same depth, so both sides work level by level and the first leaves appear in the last level: 49 440
+    nodes, 28 800 leaves, nothing order dependent). (b) With the upper bound AT the best leaf found in (a) and small
+    batches: no leaf can improve it, the explored set is a constant of (seeds, bound). Counts and incumbent must be
+    identical in both."""
+    from __graft_entry__ import load_package
+    bb = load_package()
+    nj = klass(inst)
+    L = orc.oracle(nj)
+    ins = bb.Instance(inst=inst)
+    n = ins.n
+    h = L.orc_pfsp_new(inst)
+    rng = np.random.default_rng(77 * inst + lb)
+    seeds = orc.random_pfsp_nodes(rng, n, 40, n - 6, n - 6, width=2 + nj)
+
+    def checker(best0):
+        level, tree, sol, best = seeds, 0, 0, best0
+        while len(level):
+            level, t, s, best, _ = orc.oracle_one_level(h, n, lb, level, best, L=L)
+            tree, sol = tree + t, sol + s
+        return tree, sol, best
+
+    full = checker(INT_MAX)
+    assert full[0] == 40 * (6 + 30 + 120 + 360 + 720) and full[1] == 40 * 720
+    mn = full[2]
+    eng = bb.Engine.pfsp(ins, lb, M=1 << 16)
+    eng.reset(INT_MAX)
+    eng.push_nodes(seeds)
+    st = eng.run()
+    assert (st.tree, st.sol, st.best) == full
+    eng.close()
+    bounded = checker(mn)
+    assert bounded[2] == mn
+    eng = bb.Engine.pfsp(ins, lb, M=4096)
+    for _ in range(2):
+        eng.reset(mn)
+        eng.push_nodes(seeds)
+        st = eng.run()
+        assert (st.tree, st.sol, st.best) == bounded
+    # small batches without an upper bound: the tree is order dependent, the optimum below the seeds is not
+    eng.reset(INT_MAX)
+    eng.push_nodes(seeds)
+    assert eng.run().best == mn
+    eng.close()
+    L.orc_pfsp_free(h)
