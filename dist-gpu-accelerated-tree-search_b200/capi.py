@@ -10,9 +10,10 @@ LIB_PATH = os.path.join(_HERE, "libbbgpu.so")
 MAX_JOBS = 20
 MAX_MACHINES = 20
 MAX_QUEENS = 20
-MAX_JOBS_WIDE = 100
+MAX_JOBS_WIDE = 200
 NODE_I16_WIDE = 2 + 50  # the reference's Node when built with MAX_JOBS 50 (engines of 21..50-job instances)
 NODE_I16_WIDE100 = 2 + 100  # ... with MAX_JOBS 100 (engines of 51..100-job instances)
+NODE_I16_WIDE200 = 2 + 200  # ... with MAX_JOBS 200 (engines of 101..200-job instances)
 NODE_I16 = 2 + MAX_JOBS     # reference PFSP Node: int16 depth, limit1, prmu[20]  (pfsp/lib/PFSP_node.h:15-20)
 NQ_REC = 1 + MAX_QUEENS     # reference N-Queens Node: uint8 depth, board[20]     (nqueens/lib/NQueens_node.h:13-17)
 INT_MAX = 2**31 - 1
@@ -239,7 +240,8 @@ class Engine:
     def pfsp(cls, instance, lb, **cfg):
         e = cls(lib.bb_pfsp_engine_create(instance.ptr, lb, C.byref(default_config(**cfg))), "pfsp")
         e.instance = instance  # keep the host tables alive
-        e.node_i16 = NODE_I16 if instance.n <= MAX_JOBS else NODE_I16_WIDE if instance.n <= 50 else NODE_I16_WIDE100
+        e.node_i16 = (NODE_I16 if instance.n <= MAX_JOBS else NODE_I16_WIDE if instance.n <= 50
+                      else NODE_I16_WIDE100 if instance.n <= 100 else NODE_I16_WIDE200)
         return e
 
     @classmethod

@@ -95,7 +95,7 @@ struct bb_engine
   void *g16_mem;
   int staged, stage_a; /* LB2: staged kernel with learned pair order (bb_pfsp_lb2.cuh), pairs tried in stage A */
   unsigned long long table_bytes;
-  /* PFSP, 21..100 jobs (bb_pfsp_wide.cuh): wider record, its own tables; 0, or the job-capacity class 50 / 100 */
+  /* PFSP, 21..200 jobs (bb_pfsp_wide.cuh): wider record, its own tables; 0, or the job-capacity class 50 / 100 / 200 */
   int wide;
   bb_pfsp_wide_dev TW;
   void *wide_mem;
@@ -312,7 +312,7 @@ __global__ void k_export_pfsp(int16_t *__restrict__ nodes, bb_pool pool, int sta
     nd[2 + j] = (int16_t)((w[j >> 2] >> (8 * (j & 3))) & 0xff);
 }
 
-/* 21..100 jobs: the reference's Node built with MAX_JOBS NJ (int16 depth, limit1, prmu[NJ]) <-> the wide record */
+/* 21..200 jobs: the reference's Node built with MAX_JOBS NJ (int16 depth, limit1, prmu[NJ]) <-> the wide record */
 template <int NJ>
 __global__ void k_seed_pfsp_wide(const int16_t *__restrict__ nodes, int count, bb_pool pool, bb_pfsp_wide_dev T, int at)
 {
@@ -822,11 +822,11 @@ static int upload_pfsp_tables(bb_engine *e, const bb_pfsp_instance *ins)
   return BB_OK;
 }
 
-/* 21..100 jobs: tables of bb_pfsp_wide_dev in one allocation, the wide kernel of the requested bound and class */
+/* 21..200 jobs: tables of bb_pfsp_wide_dev in one allocation, the wide kernel of the requested bound and class */
 static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, const bb_config *cfg)
 {
   e->kind = KIND_PFSP;
-  e->wide = wide_class(ins->nb_jobs); /* job-capacity class of the record and of the host's Node: 50 or 100 */
+  e->wide = wide_class(ins->nb_jobs); /* job-capacity class of the record and of the host's Node: 50, 100 or 200 */
   e->lb = lb;
   e->n = ins->nb_jobs;
   e->m = ins->nb_machines;
@@ -882,12 +882,15 @@ static int create_pfsp_wide(bb_engine *e, const bb_pfsp_instance *ins, int lb, c
   e->T.n = n; /* the generic code paths read n / m from here */
   e->T.m = m;
   e->T.P = P;
-  const void *k = NJ == 50 ? (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 50>
-                              : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 50>
-                                        : (const void *)bbk::pfsp_expand_wide<2, 50>)
-                           : (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 100>
-                              : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 100>
-                                        : (const void *)bbk::pfsp_expand_wide<2, 100>);
+  const void *k = NJ == 50    ? (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 50>
+                                 : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 50>
+                                           : (const void *)bbk::pfsp_expand_wide<2, 50>)
+                  : NJ == 100 ? (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 100>
+                                 : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 100>
+                                           : (const void *)bbk::pfsp_expand_wide<2, 100>)
+                              : (lb == 0   ? (const void *)bbk::pfsp_expand_wide<0, 200>
+                                 : lb == 1 ? (const void *)bbk::pfsp_expand_wide<1, 200>
+                                           : (const void *)bbk::pfsp_expand_wide<2, 200>);
   rc = setup_launch(e, k, bbk::wide_layout(m, NJ).total);
   if (rc)
     return rc;
@@ -1214,8 +1217,10 @@ extern "C" int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int co
     const int blocks = (count + 127) / 128;
     if (e->kind == KIND_PFSP && e->wide == 50)
       k_seed_pfsp_wide<50><<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
-    else if (e->kind == KIND_PFSP && e->wide)
+    else if (e->kind == KIND_PFSP && e->wide == 100)
       k_seed_pfsp_wide<100><<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
+    else if (e->kind == KIND_PFSP && e->wide)
+      k_seed_pfsp_wide<200><<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->TW, at);
     else if (e->kind == KIND_PFSP)
       k_seed_pfsp<<<blocks, 128, 0, e->stream>>>((const int16_t *)stage, count, e->pool, e->T, at, e->T.mp,
                                                  e->pool.nplanes);
@@ -1240,7 +1245,7 @@ extern "C" int bb_engine_push_root(bb_engine *e)
     return bb_fail(BB_ERR_ARG, "null engine");
   if (e->kind == KIND_PFSP)
   {
-    int16_t nd[2 + BB_MAX_JOBS_WIDE]; /* an engine reads the first 2 + 20 / 50 / 100 entries */
+    int16_t nd[2 + BB_MAX_JOBS_WIDE]; /* an engine reads the first 2 + 20 / 50 / 100 / 200 entries */
     memset(nd, 0, sizeof(nd));
     nd[0] = 0;
     nd[1] = -1;
@@ -1283,8 +1288,10 @@ extern "C" long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long
     const int blocks = (cnt + 127) / 128;
     if (e->kind == KIND_PFSP && e->wide == 50)
       k_export_pfsp_wide<50><<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
-    else if (e->kind == KIND_PFSP && e->wide)
+    else if (e->kind == KIND_PFSP && e->wide == 100)
       k_export_pfsp_wide<100><<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
+    else if (e->kind == KIND_PFSP && e->wide)
+      k_export_pfsp_wide<200><<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else if (e->kind == KIND_PFSP)
       k_export_pfsp<<<blocks, 128, 0, e->stream>>>((int16_t *)stage, e->pool, s, from, cnt, at);
     else if (e->nq_gen == 3)
@@ -1565,8 +1572,8 @@ int bb_engine_zero_counters(bb_engine *e)
  * the root to the same SET of nodes; it keeps the nodes whose placed prefix hashes to its id and drops the others, in
  * place, stack by stack (one CTA: the warm-up pool is a few thousand nodes). A content hash needs no communication
  * and does not depend on the order in which the device appended the nodes.
- * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4/5), 2: N-Queens plane + tail words, 3 / 4: PFSP
- * record of the 50- / 100-job classes. */
+ * mode 0: PFSP record, 1: N-Queens record with masks (nq_expand3/4/5), 2: N-Queens plane + tail words, 3 / 4 / 5: PFSP
+ * record of the 50- / 100- / 200-job classes. */
 __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, int mode, int nq_dbyte, int D, int me,
                                                    int total_warps)
 {
@@ -1580,7 +1587,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
     for (int c0 = from; c0 < to; c0 += blockDim.x)
     {
       const int i = c0 + threadIdx.x;
-      uint4 pl[wide_geom<100>::NPL]; /* the widest record */
+      uint4 pl[wide_geom<200>::NPL]; /* the widest record */
       uint32_t tw[2] = {0u, 0u};
       bool keep = false;
       if (i < to)
@@ -1600,6 +1607,8 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
           depth = (int)(pw[wide_geom<50>::W_DEPTH] & 0xffu);
         else if (mode == 4)
           depth = (int)(pw[wide_geom<100>::W_DEPTH] & 0xffu);
+        else if (mode == 5)
+          depth = (int)(pw[wide_geom<200>::W_DEPTH] & 0xffu);
         else if (mode == 0)
           depth = (int)(pl[1].y & 0xffu);
         else if (mode == 1)
@@ -1653,7 +1662,7 @@ __global__ void __launch_bounds__(1024) k_partition(bb_ctrl *c, bb_pool pool, in
 int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters)
 {
   ENGINE_SET_DEVICE(e);
-  int mode = e->wide == 50 ? 3 : e->wide ? 4 : 0, dbyte = 0;
+  int mode = e->wide == 50 ? 3 : e->wide == 100 ? 4 : e->wide ? 5 : 0, dbyte = 0;
   if (e->kind == KIND_NQ)
   {
     mode = e->nq_gen == 3 ? 1 : 2;

@@ -1,11 +1,13 @@
 /*
- * bb_pfsp_wide.cuh - fused bound -> prune -> branch -> compact for the 50- and 100-job Taillard classes
- * (ta031-ta060, ta061-ta090).
+ * bb_pfsp_wide.cuh - fused bound -> prune -> branch -> compact for the 50-, 100- and 200-job Taillard classes
+ * (ta031-ta060, ta061-ta090, ta091-ta110).
  *
  * The reference handles instances above 20 jobs by editing MAX_JOBS in pfsp/lib/macro.h:10 and rebuilding
  * (pfsp/README.md:52); its kernels and host code are otherwise the same. Here the engine switches to this kernel and
- * a wider record when an instance has 21..100 jobs (two job-capacity classes, wide_geom<50> and wide_geom<100>: the
- * reference's MAX_JOBS; the layout below is the 50-job one, the 100-job record has 25 prmu words, 4 mask words, 13 planes):
+ * a wider record when an instance has 21..200 jobs (three job-capacity classes, wide_geom<50 / 100 / 200>: the
+ * reference's MAX_JOBS; the layout below is the 50-job one, the 100-job record has 25 prmu words, 4 mask words, 13
+ * planes, the 200-job record 50 prmu words, 7 mask words, 20 planes; job ids stay 8-bit, which is why the 500-job class
+ * is not covered):
  *     words  0..12   prmu[50] as uint8 (first `depth` entries = scheduled prefix)
  *     word   13      depth
  *     words 14..15   scheduled-set bitmask (64 bits)
@@ -27,24 +29,27 @@
 
 #include "bb_pfsp_kernels.cuh"
 
-/* record geometry of a job-capacity class NJ (50: ta031-ta060, 100: ta061-ta090), in 32-bit words */
+/* record geometry of a job-capacity class NJ (50: ta031-ta060, 100: ta061-ta090, 200: ta091-ta110), in 32-bit words */
 template <int NJ>
 struct wide_geom
 {
-  static_assert(NJ == 50 || NJ == 100, "job-capacity classes of the wide kernel");
+  static_assert(NJ == 50 || NJ == 100 || NJ == 200, "job-capacity classes of the wide kernel");
   static constexpr int JOBS = NJ;
-  static constexpr int STRIDE = NJ == 50 ? 64 : 128; /* jobs / Johnson slots per row in the wide tables */
-  static constexpr int PRW = (NJ + 3) / 4;           /* words of prmu[]: 13 / 25 */
-  static constexpr int W_DEPTH = PRW;                /* 13 / 25 */
-  static constexpr int W_MASK = PRW + 1;             /* 14 / 26 */
-  static constexpr int MW = (NJ + 31) / 32;          /* words of the scheduled-set bitmask: 2 / 4 */
-  static constexpr int W_FRONT = W_MASK + MW;        /* 16 / 30 */
-  static constexpr int W_REMAIN = W_FRONT + BB_MAX_MACHINES / 2; /* 26 / 40 */
-  static constexpr int NPL = (W_REMAIN + BB_MAX_MACHINES / 2 + 3) / 4; /* planes of 16 bytes: 9 / 13 */
+  static constexpr int STRIDE = NJ == 50 ? 64 : NJ == 100 ? 128 : 256; /* jobs / Johnson slots per row in the wide tables */
+  static constexpr int PRW = (NJ + 3) / 4;           /* words of prmu[]: 13 / 25 / 50 */
+  static constexpr int W_DEPTH = PRW;                /* 13 / 25 / 50 */
+  static constexpr int W_MASK = PRW + 1;             /* 14 / 26 / 51 */
+  static constexpr int MW = (NJ + 31) / 32;          /* words of the scheduled-set bitmask: 2 / 4 / 7 */
+  static constexpr int W_FRONT = W_MASK + MW;        /* 16 / 30 / 58 */
+  static constexpr int W_REMAIN = W_FRONT + BB_MAX_MACHINES / 2; /* 26 / 40 / 68 */
+  static constexpr int NPL = (W_REMAIN + BB_MAX_MACHINES / 2 + 3) / 4; /* planes of 16 bytes: 9 / 13 / 20 */
 };
-__host__ __device__ inline int wide_class(int n) { return n <= 50 ? 50 : 100; }
-__host__ __device__ inline int wide_stride(int nj) { return nj == 50 ? 64 : 128; }
-__host__ __device__ inline int wide_planes(int nj) { return nj == 50 ? wide_geom<50>::NPL : wide_geom<100>::NPL; }
+__host__ __device__ inline int wide_class(int n) { return n <= 50 ? 50 : n <= 100 ? 100 : 200; }
+__host__ __device__ inline int wide_stride(int nj) { return nj == 50 ? 64 : nj == 100 ? 128 : 256; }
+__host__ __device__ inline int wide_planes(int nj)
+{
+  return nj == 50 ? wide_geom<50>::NPL : nj == 100 ? wide_geom<100>::NPL : wide_geom<200>::NPL;
+}
 
 /* instance tables of a wide engine (device global memory) */
 struct bb_pfsp_wide_dev

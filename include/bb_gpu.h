@@ -25,11 +25,11 @@ extern "C" {
 #endif
 
 #define BB_MAX_JOBS 20     /* pfsp/lib/macro.h:10 */
-#define BB_MAX_JOBS_WIDE 100 /* the 50- and 100-job Taillard classes ta031-ta090: the reference rebuilt with MAX_JOBS
-                                50 / 100 (pfsp/README.md:52). Engines of such instances exchange nodes with the host as
-                                that build's Node: int16 [depth, limit1, prmu[50]] for 21..50 jobs, int16 [depth,
-                                limit1, prmu[100]] for 51..100 jobs; the compat level stays at 20 */
-#define BB_NODE_JOBS(n) ((n) <= BB_MAX_JOBS ? BB_MAX_JOBS : (n) <= 50 ? 50 : 100) /* prmu[] entries of a host node */
+#define BB_MAX_JOBS_WIDE 200 /* the 50-, 100- and 200-job Taillard classes ta031-ta110: the reference rebuilt with
+                                MAX_JOBS 50 / 100 / 200 (pfsp/README.md:52). Engines of such instances exchange nodes
+                                with the host as that build's Node: int16 [depth, limit1, prmu[NJ]] with NJ = 50 for
+                                21..50 jobs, 100 for 51..100, 200 for 101..200; the compat level stays at 20 */
+#define BB_NODE_JOBS(n) ((n) <= BB_MAX_JOBS ? BB_MAX_JOBS : (n) <= 50 ? 50 : (n) <= 100 ? 100 : 200) /* prmu[] entries of a host node */
 #define BB_MAX_MACHINES 20 /* pfsp/lib/macro.h:11 */
 #define BB_MAX_QUEENS 20   /* nqueens/lib/NQueens_node.h:11 */
 
@@ -204,9 +204,9 @@ typedef struct bb_stats
 void bb_config_default(bb_config *cfg);
 
 /* lb: 0 LB1_d, 1 LB1, 2 LB2 (PFSP_lib.c:225-232). Uploads the tables (a6) and allocates the pool. Instances with up
- * to 20 jobs run the tuned kernels; 21..100 jobs (ta031-ta090) run a wider record and kernel in two job-capacity classes,
- * 50 and 100 (LB2 as the machine-pair loop: a 2^n table does not exist there); more than 100 jobs or 20 machines are
- * refused. */
+ * to 20 jobs run the tuned kernels; 21..200 jobs (ta031-ta110) run a wider record and kernel in three job-capacity
+ * classes, 50, 100 and 200 (LB2 as the machine-pair loop: a 2^n table does not exist there); more than 200 jobs (the
+ * 500-job class ta111-ta120: job ids no longer fit the record's bytes) or 20 machines are refused. */
 bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb, const bb_config *cfg);
 bb_engine *bb_nq_engine_create(int N, int G, const bb_config *cfg);
 void bb_engine_destroy(bb_engine *e);

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
-"""tests/golden/wide.json: golden vectors for the 50- and 100-job Taillard classes from the REFERENCE rebuilt with
-MAX_JOBS 50 / 100 (oracle/_ref/libref_pfsp<NJ>.so and oracle/_ref/pfsp_c<NJ>.out, `make -C oracle ref50 ref100`:
+"""tests/golden/wide.json: golden vectors for the 50-, 100- and 200-job Taillard classes from the REFERENCE rebuilt with
+MAX_JOBS 50 / 100 / 200 (oracle/_ref/libref_pfsp<NJ>.so, oracle/_ref/pfsp_c<NJ>.out, `make -C oracle ref50 ref100 ref200`:
 pfsp/README.md:52 asks for exactly that edit). Table hashes, the bounds[] a chunk of random parents gets from
 lb1_children_bounds / lb1_bound / lb2_bound (c_bound_simple.c:143-244, c_bound_johnson.c:239-254) in evaluate_gpu's
 layout, and the printed counts of the instances the reference solves at the root. Run in the build container:
@@ -19,19 +19,19 @@ sys.path.insert(0, os.path.dirname(HERE))
 import orc  # noqa: E402
 
 def klass(inst):
-    return 50 if inst <= 60 else 100
+    return 50 if inst <= 60 else 100 if inst <= 90 else 200
 
 
 def main():
-    out = {"what": "reference rebuilt with MAX_JOBS 50 / 100 (make -C oracle ref50 ref100); see make_golden_wide.py"}
-    for inst in (31, 41, 51, 61, 71, 81):
+    out = {"what": "reference rebuilt with MAX_JOBS 50 / 100 / 200 (make -C oracle ref50 ref100 ref200); see make_golden_wide.py"}
+    for inst in (31, 41, 51, 61, 71, 81, 91, 101):
         R = orc.ref_pfsp(klass(inst))
         W = 2 + klass(inst)
         t = orc.ref_tables_of(R, inst)
         r = R.ref_pfsp_open(inst)
         n, best = t.n, t.best_ub
         rng = np.random.default_rng(7000 + inst)
-        parents = orc.random_pfsp_nodes(rng, n, 24 if inst <= 60 else 10, 0, n - 2, width=W)
+        parents = orc.random_pfsp_nodes(rng, n, 24 if inst <= 60 else 10 if inst <= 90 else 5, 0, n - 2, width=W)
         bounds = {"0": [], "1": [], "2": []}
         for nd in parents:
             d = int(nd[0])
@@ -51,7 +51,7 @@ def main():
     runs = []
     # ta034 under LB1_d and most 100-job instances do not finish in minutes on a CPU; these are solved at the root
     for inst, lb in ((32, 0), (32, 1), (32, 2), (34, 2), (66, 0), (66, 1), (66, 2), (69, 0), (69, 2), (63, 2), (65, 2),
-                     (61, 2)):
+                     (61, 2), (94, 0), (94, 2), (97, 0), (97, 1), (97, 2), (100, 0), (100, 2)):
         exe = os.path.join(orc.REF_DIR, "pfsp_c%d.out" % klass(inst))
         txt = subprocess.run([exe, "-i", str(inst), "-l", str(lb), "-u", "1"], capture_output=True, text=True,
                              cwd="/tmp", timeout=120).stdout

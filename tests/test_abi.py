@@ -85,8 +85,8 @@ def test_op_model_matches_reference_formulas():
 
 
 def test_unsupported_sizes_are_refused_loudly():
-    ins = bb.Instance(inst=91)  # 200 jobs: beyond the 50- and 100-job classes this build covers (pfsp/README.md:52)
-    with pytest.raises(bb.BBError, match="200 jobs"):
+    ins = bb.Instance(inst=111)  # 500 jobs: beyond the 50-, 100- and 200-job classes this build covers (pfsp/README.md:52)
+    with pytest.raises(bb.BBError, match="500 jobs"):
         bb.Engine.pfsp(ins, 0)
     with pytest.raises(bb.BBError):
         bb.Engine.nqueens(21)

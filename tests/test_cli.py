@@ -38,11 +38,11 @@ def test_pfsp_flag_validation_matches_reference(args, msg, tmp_path):
 def test_pfsp_settings_block_and_refusals(tmp_path):
     r = run(PFSP, "-C", 2, cwd=tmp_path)  # pfsp_multigpu_cuda.c:523-527
     assert r.returncode == 1 and r.stdout.startswith("C is set to 2. Invalid option for this version.")
-    r = run(PFSP, "--inst", 91, "--lb", 0, "--ub", 0, "-C", 0, "-w", 0, cwd=tmp_path)  # 200 jobs: refused loudly
-    assert r.returncode == 1 and "supports at most 100 x 20" in r.stderr
+    r = run(PFSP, "--inst", 111, "--lb", 0, "--ub", 0, "-C", 0, "-w", 0, cwd=tmp_path)  # 500 jobs: refused loudly
+    assert r.returncode == 1 and "supports at most 200 x 20" in r.stderr
     assert r.stdout == ("\n=================================================\n"
                         "Multi-core Multi-GPU C+OpenMP+CUDA (1 GPU(s) - [0] Multi-core - [0] Work Stealing)\n\n"
-                        "Resolution of PFSP Taillard's instance: ta91 (m = 10, n = 200)\n"
+                        "Resolution of PFSP Taillard's instance: ta111 (m = 20, n = 500)\n"
                         "Initial upper bound: inf\nLower bound function: lb1_d\nBranching rule: fwd\n"
                         "=================================================\n")
 
@@ -69,9 +69,10 @@ def parse_final(out):
 @pytest.mark.parametrize("args,exp", [(["-i", 14, "-l", 1], (2573652, 2648, 1377)), (["-i", 14, "-l", 0], (2573652, 2648, 1377)),
                                       (["-i", 14, "-l", 2, "-M", 100000], (144639, 0, 1377)),
                                       (["-i", 2, "-l", 2, "-C", 0], (7, 0, 1359)),
-                                      # 50- and 100-job classes: what the reference rebuilt with MAX_JOBS 50 / 100 prints
+                                      # 50-, 100- and 200-job classes: what the reference rebuilt with MAX_JOBS 50 / 100 / 200 prints
                                       (["-i", 32, "-l", 2, "-C", 0], (3, 0, 2834)),
-                                      (["-i", 66, "-l", 0, "-C", 0], (11, 0, 5135))])
+                                      (["-i", 66, "-l", 0, "-C", 0], (11, 0, 5135)),
+                                      (["-i", 94, "-l", 2, "-C", 0], (55, 0, 10889))])
 def test_pfsp_run_prints_reference_counts_and_csv(args, exp, tmp_path, golden):
     r = run(PFSP, *args, cwd=tmp_path)
     assert r.returncode == 0, r.stderr

@@ -1,7 +1,7 @@
-"""The 50- and 100-job Taillard classes (ta031-ta090). The reference handles them by editing MAX_JOBS in
+"""The 50-, 100- and 200-job Taillard classes (ta031-ta110). The reference handles them by editing MAX_JOBS in
 pfsp/lib/macro.h:10 and rebuilding (pfsp/README.md:52); the checker is the same restatement built with 50- / 100-job
-node records (oracle/liboracle50.so, liboracle100.so), pinned here against that rebuilt reference
-(oracle/_ref/libref_pfsp<NJ>.so, make -C oracle ref50 ref100) where it is present, and against tests/golden/wide.json
+node records (oracle/liboracle50.so, liboracle100.so, liboracle200.so), pinned here against that rebuilt reference
+(oracle/_ref/libref_pfsp<NJ>.so, make -C oracle ref50 ref100 ref200) where it is present, and against tests/golden/wide.json
 (generated from it by tests/golden/make_golden_wide.py) everywhere. The GPU tests compare the engine's wide kernel with
 the checker through the C ABI: the child SET of one iteration for all three bounds, and whole searches."""
 import ctypes as C
@@ -17,7 +17,7 @@ INT_MAX = 2**31 - 1
 
 def klass(inst):
     """job-capacity class of a Taillard instance: MAX_JOBS of the reference build that handles it"""
-    return 50 if inst <= 60 else 100
+    return 50 if inst <= 60 else 100 if inst <= 90 else 200
 
 
 def chunk_bounds(L, h, n, lb, parents, best):
@@ -31,7 +31,7 @@ def golden_nodes(g, inst):
     return np.array(g["parents"], dtype=np.int16).reshape(-1, 2 + klass(inst))
 
 
-@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81])
+@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81, 91, 101])
 def test_wide_oracle_matches_reference_golden(inst):
     """tables and chunk-level bounds of the 50- / 100-job checker against what the rebuilt reference produced"""
     g = load_golden("wide")[str(inst)]
@@ -49,7 +49,7 @@ def test_wide_oracle_matches_reference_golden(inst):
     L.orc_pfsp_free(h)
 
 
-@pytest.mark.parametrize("inst", [31, 45, 52, 62, 77, 84])
+@pytest.mark.parametrize("inst", [31, 45, 52, 62, 77, 84, 93, 108])
 def test_wide_oracle_matches_reference_directly(inst):
     if not orc.have_ref_wide(klass(inst)):
         pytest.skip("oracle/_ref/libref_pfsp%d.so not built (make -C oracle ref%d)" % (klass(inst), klass(inst)))
@@ -79,7 +79,7 @@ def test_wide_oracle_matches_reference_directly(inst):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(240, method="thread")
-@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81])
+@pytest.mark.parametrize("inst", [31, 41, 51, 61, 71, 81, 91, 101])
 @pytest.mark.parametrize("lb", [0, 1, 2])
 def test_wide_one_iteration_children_match_oracle(inst, lb):
     from __graft_entry__ import load_package
@@ -92,7 +92,7 @@ def test_wide_one_iteration_children_match_oracle(inst, lb):
     rng = np.random.default_rng(1000 * inst + lb)
     eng = bb.Engine.pfsp(ins, lb, M=100000)
     for best in (ins.best_known, ins.best_known + 400):
-        parents = orc.random_pfsp_nodes(rng, n, 3000 if n <= 50 else 1200, 0, n - 2, width=W)
+        parents = orc.random_pfsp_nodes(rng, n, 3000 if n <= 50 else 1200 if n <= 100 else 400, 0, n - 2, width=W)
         parents[0, :2] = (0, -1)
         parents[0, 2:2 + n] = np.arange(n)
         eng.reset(best)
@@ -109,7 +109,7 @@ def test_wide_one_iteration_children_match_oracle(inst, lb):
 
 @pytest.mark.gpu
 @pytest.mark.timeout(240, method="thread")
-@pytest.mark.parametrize("nj", [50, 100])
+@pytest.mark.parametrize("nj", [50, 100, 200])
 def test_wide_whole_searches_match_oracle(nj):
     """whole trees: the instances the reference solves at the root (ta032, ta034, ta061, ta063, ta065, ta066, ta069:
     counts printed by the rebuilt pfsp_c, tests/golden/wide.json), and searches of ta031 / ta041 / ta051 (ta061 / ta071
@@ -125,8 +125,9 @@ def test_wide_whole_searches_match_oracle(nj):
         res, per = bb.pfsp_search(bb.Instance(inst=r["inst"]), r["lb"], M=1 << 16)
         assert (res.tree, res.sol, res.best) == (r["tree"], r["sol"], r["makespan"]), r
     rng = np.random.default_rng(5 + nj)
-    cases = [(bb.Instance(inst=i), L.orc_pfsp_new(i)) for i in ((31, 41, 51) if nj == 50 else (61, 71, 81))]
-    for n, m in (((26, 5), (33, 10), (40, 7)) if nj == 50 else ((60, 5), (75, 10), (90, 7))):
+    cases = [(bb.Instance(inst=i), L.orc_pfsp_new(i))
+             for i in {50: (31, 41, 51), 100: (61, 71, 81), 200: (91, 101)}[nj]]
+    for n, m in {50: ((26, 5), (33, 10), (40, 7)), 100: ((60, 5), (75, 10), (90, 7)), 200: ((130, 5), (180, 12))}[nj]:
         p = rng.integers(1, 100, size=(m, n)).astype(np.int32)
         cases.append((bb.Instance(p_times=p), L.orc_pfsp_from_ptimes(n, m, np.ascontiguousarray(p.reshape(-1)))))
     compared = 0
@@ -140,19 +141,20 @@ def test_wide_whole_searches_match_oracle(nj):
         for lb in (0, 1, 2):
             for delta in (3, 12, 30):
                 best0 = base + delta
-                L.orc_pfsp_search(h, lb, best0, 400_000 if nj == 50 else 150_000, C.byref(st))
-                if st.parents >= (400_000 if nj == 50 else 150_000) or st.best != best0:
+                budget = {50: 400_000, 100: 150_000, 200: (150_000, 5_000, 1_000)[lb]}[nj]  # the checker's LB2 is O(n^2 m^2)
+                L.orc_pfsp_search(h, lb, best0, budget, C.byref(st))
+                if st.parents >= budget or st.best != best0:
                     break  # the checker's budget ran out, or a leaf improved the bound: not a constant tree
                 res, per = bb.pfsp_search(ins, lb, best0=best0, M=1 << 14)
                 assert (res.tree, res.sol, res.best) == (st.tree, st.sol, best0), (n, ins.m, lb, delta)
                 compared += 1
         L.orc_pfsp_free(h)
-    assert compared >= (12 if nj == 50 else 6)
+    assert compared >= {50: 12, 100: 6, 200: 3}[nj]
 
 
 @pytest.mark.gpu
 @pytest.mark.timeout(240, method="thread")
-@pytest.mark.parametrize("inst", [41, 51, 71, 81])
+@pytest.mark.parametrize("inst", [41, 51, 71, 81, 91, 101])
 @pytest.mark.parametrize("lb", [0, 1, 2])
 def test_wide_subtrees_below_deep_seeds_match_oracle(inst, lb):
     """searches to exhaustion that are not trivial at 50 / 100 jobs: 40 random nodes with six jobs left are seeded and
