@@ -106,6 +106,7 @@ EXPORTS = [
     "bb_pfsp_instance_taillard", "bb_pfsp_instance_from_ptimes", "bb_pfsp_instance_free", "bb_config_default",
     "bb_pfsp_engine_create", "bb_nq_engine_create", "bb_engine_destroy", "bb_release_cached_memory", "bb_engine_reset", "bb_engine_push_root",
     "bb_engine_push_nodes", "bb_engine_export_nodes", "bb_engine_set_best", "bb_engine_get_stats", "bb_engine_run",
+    "bb_engine_keep_share",
     "bb_pfsp_search", "bb_nq_search", "bb_pfsp_expand_static", "bb_pfsp_search_dist", "bb_nq_search_dist", "bb_pfsp_dist_open", "bb_nq_dist_open", "bb_dist_search",
     "bb_dist_close",
     "bb_team_bytes", "bb_team_init", "bb_team_reset", "bb_team_wait_ready", "bb_team_barrier", "bb_team_fail", "bb_team_worker",
@@ -130,6 +131,7 @@ lib.bb_release_cached_memory.argtypes = [C.c_int]
 lib.bb_engine_reset.argtypes = [_vp, C.c_int]
 lib.bb_engine_push_root.argtypes = [_vp]
 lib.bb_engine_push_nodes.argtypes = [_vp, _vp, C.c_int]
+lib.bb_engine_keep_share.argtypes = [_vp, C.c_int, C.c_int]
 lib.bb_engine_export_nodes.restype = C.c_longlong
 lib.bb_engine_export_nodes.argtypes = [_vp, _vp, C.c_longlong]
 lib.bb_engine_set_best.argtypes = [_vp, C.c_int]
@@ -271,6 +273,9 @@ class Engine:
 
     def set_best(self, best):
         check(lib.bb_engine_set_best(self.h, best), "bb_engine_set_best")
+
+    def keep_share(self, parts, me):
+        check(lib.bb_engine_keep_share(self.h, parts, me), "bb_engine_keep_share")
 
     def stats(self):
         st = Stats()

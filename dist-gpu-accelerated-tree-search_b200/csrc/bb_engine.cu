@@ -1675,6 +1675,16 @@ int bb_engine_partition(bb_engine *e, int D, int me, int zero_counters)
   return BB_OK;
 }
 
+extern "C" int bb_engine_keep_share(bb_engine *e, int parts, int me)
+{
+  if (!e || parts < 1 || me < 0 || me >= parts)
+    return bb_fail(BB_ERR_ARG, "bb_engine_keep_share: bad engine or share %d of %d", me, parts);
+  int rc = bb_engine_partition(e, parts, me, 0);
+  if (rc)
+    return rc;
+  return fetch_ctrl(e);
+}
+
 int bb_engine_kind_is_pfsp(const bb_engine *e) { return e->kind == KIND_PFSP; }
 
 /* ------------------------------------------------------------------ the device loop */

@@ -225,6 +225,11 @@ int bb_engine_push_nodes(bb_engine *e, const void *host_nodes, int count);
 long long bb_engine_export_nodes(bb_engine *e, void *host_nodes, long long max_count);
 int bb_engine_set_best(bb_engine *e, int best);
 int bb_engine_get_stats(bb_engine *e, bb_stats *out);
+/* Keep this engine's share of the pool, on the device and in place: the nodes whose placed prefix hashes to `me`
+ * of `parts` (FNV-1a over the scheduled jobs / placed rows), dropping the others. D engines that hold the same set of
+ * nodes and each call this with their own `me` end up with disjoint shares whose union is the set - the warm-up split
+ * of the multi-GPU searches (replaces roundRobin_distribution, Pool_atom.c:14-36) without any communication. */
+int bb_engine_keep_share(bb_engine *e, int parts, int me);
 
 /* Run device iterations until the pool is empty (max_iters <= 0) or max_iters iterations were done. */
 int bb_engine_run(bb_engine *e, long long max_iters, bb_stats *out);
