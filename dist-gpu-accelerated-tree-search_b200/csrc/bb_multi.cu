@@ -268,8 +268,14 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
     return search_single(kind, ins, lb, best0, N, G, cfg, res, per_gpu);
   int ndev = 0;
   BB_CUDA_TRY(cudaGetDeviceCount(&ndev));
-  if (D > ndev || D > 64)
+  /* BB_WORKERS_SHARE_GPUS=1: more workers than GPUs, worker i on GPU i mod visible. The team protocol, the warm-up
+   * split, donations and pulls run exactly as across GPUs (the "peer" buffer is then a buffer of the same device);
+   * it exists so that the multi-worker paths can be exercised on a one-GPU box, not for speed. */
+  const bool share = getenv("BB_WORKERS_SHARE_GPUS") != nullptr && ndev > 0;
+  if ((D > ndev && !share) || D > 64)
     return bb_fail(BB_ERR_ARG, "%d GPUs requested, %d visible", D, ndev); /* pfsp_multigpu_cuda.c:539-543 */
+  auto dev_of = [ndev](int worker) { return worker % ndev; };
+  const int used_dev = D < ndev ? D : ndev;
   bb_config c;
   if (cfg)
     c = *cfg;
@@ -285,7 +291,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
     std::vector<int> irc(D, 0);
     for (int i = 0; i < D; i++)
       init.emplace_back([&, i]() {
-        if (cudaSetDevice(i) != cudaSuccess || cudaFree(nullptr) != cudaSuccess)
+        if (cudaSetDevice(dev_of(i)) != cudaSuccess || cudaFree(nullptr) != cudaSuccess)
           irc[i] = 1;
       });
     for (auto &t : init)
@@ -294,8 +300,8 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       if (irc[i])
         return bb_fail(BB_ERR_CUDA, "could not initialise GPU %d", i);
   }
-  for (int i = 0; i < D; i++)
-    for (int j = 0; j < D; j++)
+  for (int i = 0; i < used_dev; i++)
+    for (int j = 0; j < used_dev; j++)
       if (i != j)
       {
         BB_CUDA_TRY(cudaSetDevice(i));
@@ -329,7 +335,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         bb_team_fail(team);
       };
       const double c0 = now_s();
-      w.e = create_engine(kind, ins, lb, N, G, &c, i);
+      w.e = create_engine(kind, ins, lb, N, G, &c, dev_of(i));
       if (!w.e)
         fail(BB_ERR_CUDA);
       else if (bb_engine_stage_alloc(w.e, BB_STAGE_BYTES) != BB_OK)
@@ -348,7 +354,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       int best = best0;
       /* the search is timed from the root: warm-up expansion and partition are inside the span */
       const double s0 = now_s();
-      cudaSetDevice(i);
+      cudaSetDevice(dev_of(i));
       device_span span;
       span.begin();
       int rc = seed_partition(w.e, kind, D, i, m_keep, best0, &o.base_tree, &o.base_sol, &best);
@@ -359,7 +365,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
       {
         bb_team_ops ops = gpu_ops(&w);
         rc = bb_team_worker(team, i, &ops, ws, m_keep, 5 * M, best, c.iters_per_launch, &o.tr);
-        cudaSetDevice(i);
+        cudaSetDevice(dev_of(i));
         o.search_s = span.end_s(now_s() - s0);
         if (rc)
           fail(rc);

@@ -149,6 +149,63 @@ def test_multi_gpu_threads_same_counts(D):
     assert (res.tree, res.sol) == (171129071, 2279184)
 
 
+@pytest.mark.parametrize("D", [2, 3])
+def test_several_workers_on_one_gpu_same_counts(D, monkeypatch):
+    """the multi-worker paths on a one-GPU box: with BB_WORKERS_SHARE_GPUS the D workers of a search run on GPU
+    i mod visible. Everything else is the multi-GPU code: common warm-up, device-side split by prefix hash, host
+    protocol, donations enqueued on the victim's stream, pulls out of the victim's transfer buffer, incumbent exchange,
+    termination. Counts must be those of one worker; with work stealing off the static split alone must be complete."""
+    monkeypatch.setenv("BB_WORKERS_SHARE_GPUS", "1")
+    for ws in (1, 0):
+        res, per = bb.pfsp_search(bb.Instance(inst=30), 0, D=D, ws=ws, M=1 << 16)
+        assert (res.tree, res.sol, res.best) == (111887480, 82, 2178)
+        assert sum(p.tree for p in per) + res.warm_tree == res.tree
+        assert all(p.tree > 0 for p in per)  # every worker got a share
+        res, per = bb.pfsp_search(bb.Instance(inst=29), 2, D=D, ws=ws, M=1 << 16)
+        assert (res.tree, res.sol, res.best) == (9499307, 0, 2237)
+    res, per = bb.nq_search(14, 1, D=D, M=1 << 16)
+    assert (res.tree, res.sol) == (27358552, 365596)
+    assert all(p.tree > 0 for p in per)
+    # incumbents are exchanged between the workers (checkBest, pfsp_multigpu_cuda.c:30-50)
+    for inst, lb, opt in ((14, 2, 1377), (3, 0, 1081)):
+        res, _ = bb.pfsp_search(bb.Instance(inst=inst), lb, best0=INT_MAX, D=D, M=1 << 14)
+        assert res.best == opt
+    # a 100-job instance through the wide record (solved during the warm-up: the reference prints 11 nodes)
+    res, _ = bb.pfsp_search(bb.Instance(inst=66), 0, D=D, M=1 << 14)
+    assert (res.tree, res.sol, res.best) == (11, 0, 5135)
+
+
+def test_process_per_worker_team_on_one_gpu_same_counts():
+    """the process-per-GPU path of bench.py --gpus N (bb_*_dist_open / bb_dist_search: shared-memory team block, CUDA
+    IPC mappings of the peers' transfer buffers, persistent contexts) with two processes that both use GPU 0: every
+    search returns the one-worker counts on every rank, with and without work stealing, for PFSP, -u 0 and N-Queens"""
+    import json
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    shm = f"/bbtest_{os.getpid()}_2p"
+    procs = [subprocess.Popen([sys.executable, os.path.join(here, "dist_rank.py"), str(r), "2", shm, "0"],
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(2)]
+    outs = []
+    for p in procs:
+        try:
+            o, e = p.communicate(timeout=300)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        assert p.returncode == 0, e[-2000:]
+        outs.append(json.loads(o.strip().splitlines()[-1]))
+    for o in outs:
+        for k in ("ta030_lb1d_0", "ta030_lb1d_1", "ta030_lb1d_static"):
+            assert o[k][:3] == [111887480, 82, 2178], (k, o[k])
+            assert o[k][3] == 1  # this rank explored a share itself
+        assert o["ta014_lb2_u0_best"] == 1377
+        assert o["ta014_lb2"] == [144639, 0, 1377]
+        assert o["nq14"][:2] == [27358552, 365596] and o["nq14"][2] == 1
+
+
 @pytest.mark.parametrize("inst,lb,opt", [(14, 2, 1377), (3, 0, 1081), (14, 1, 1377)])
 def test_search_from_infinite_upper_bound_finds_the_optimum(inst, lb, opt):
     """-u 0 (PFSP_lib.c:234-241): the incumbent starts at INT_MAX and is improved by leaves through the device
