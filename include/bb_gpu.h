@@ -206,7 +206,8 @@ void bb_config_default(bb_config *cfg);
 /* lb: 0 LB1_d, 1 LB1, 2 LB2 (PFSP_lib.c:225-232). Uploads the tables (a6) and allocates the pool. Instances with up
  * to 20 jobs run the tuned kernels; 21..200 jobs (ta031-ta110) run a wider record and kernel in three job-capacity
  * classes, 50, 100 and 200 (LB2 as the machine-pair loop: a 2^n table does not exist there); more than 200 jobs (the
- * 500-job class ta111-ta120: job ids no longer fit the record's bytes) or 20 machines are refused. */
+ * 500-job class ta111-ta120: job ids no longer fit the record's bytes, and the reference's GPU path narrows the depth to
+ * uint8_t, PFSP_lib.h:60) or 20 machines are refused. */
 bb_engine *bb_pfsp_engine_create(const bb_pfsp_instance *ins, int lb, const bb_config *cfg);
 bb_engine *bb_nq_engine_create(int N, int G, const bb_config *cfg);
 void bb_engine_destroy(bb_engine *e);
