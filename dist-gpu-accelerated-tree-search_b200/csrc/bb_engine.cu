@@ -102,6 +102,8 @@ struct bb_engine
   /* N-Queens */
   int N, G;
   int nq_gen; /* 3 = masks travel with the node (nq_expand3, 32-byte record), 2 / 1 = earlier kernels (board + depth) */
+  int nq_tail; /* nq_expand5: parents with at most this many columns left are enumerated in registers (0 = never) */
+  int nq_arg;  /* the kernel's last argument: G, with nq_tail << 16 for nq_expand5 */
   /* launch */
   const void *kernel;
   bool pdl; /* the kernel waits for its predecessor itself (pdl_wait_then_release): chained with programmatic launch */
@@ -135,7 +137,7 @@ extern "C" void bb_config_default(bb_config *cfg)
   cfg->lb2_staged = 1;
   cfg->lb2_stage_a = 8;
   cfg->lb2_table = 1;
-  cfg->packed = 2;
+  cfg->packed = 3;
 }
 
 /* ------------------------------------------------------------------ small kernels: plan / seed / export */
@@ -632,7 +634,8 @@ static int launch_expand(bb_engine *e, cudaStream_t s)
   }
   else
   {
-    void *args[] = {&e->ctrl, &e->pool, &e->N, &e->G};
+    e->nq_arg = e->G | (e->nq_tail << 16);
+    void *args[] = {&e->ctrl, &e->pool, &e->N, &e->nq_arg};
     BB_CUDA_TRY(cudaLaunchKernelExC(&lc, e->kernel, args));
   }
   return BB_OK;
@@ -998,9 +1001,26 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
     if (rc)
       return rc;
     const bool c_nq5 = getenv("BB_NQ_CTA_ROUNDS") == nullptr; /* debugging aid: nq_expand4 reserves per CTA round */
+    /* packed = 2: every node goes through the pool (one launch = one level of every popped parent); packed = 3 (the
+     * default): the last levels are enumerated in registers. BB_NQ_TAIL overrides the number of levels (tuning aid). */
+    e->nq_tail = 0;
+    if (c_nq4 && c_nq5 && cfg && (cfg->packed >= 3 || cfg->packed < 0))
+    {
+      e->nq_tail = 8;
+      if (const char *t = getenv("BB_NQ_TAIL"))
+        e->nq_tail = atoi(t);
+      if (e->nq_tail > NQ5_MAX_TAIL)
+        e->nq_tail = NQ5_MAX_TAIL;
+      if (e->nq_tail < 0)
+        e->nq_tail = 0;
+    }
+    if (!cfg && c_nq4 && c_nq5)
+      e->nq_tail = 8;
+    if (G > 0xffff)
+      e->nq_tail = 0; /* the kernel argument has 16 bits for G next to the tail */
     rc = setup_launch(e,
                       !c_nq4  ? (const void *)bbk::nq_expand3
-                      : c_nq5 ? (const void *)bbk::nq_expand5
+                      : c_nq5 ? (e->nq_tail ? (const void *)bbk::nq_expand5<1> : (const void *)bbk::nq_expand5<0>)
                               : (const void *)bbk::nq_expand4,
                       0);
     e->pdl = c_nq4 && c_nq5;

@@ -56,7 +56,8 @@ struct __align__(256) bb_ctrl
   int don_stack, don_from, don_count;
   unsigned int next_round; /* dynamic hand-out of tiles to warps (nq_expand5); lives here, away from the cursor's
                             * line: the plan is only read at the start of a launch */
-  int pad0[15];
+  unsigned int next_deep;  /* nq_expand5<1>, pass A: next chunk of the batch to hand to a warp */
+  int pad0[14];
   /* ---- second line: what every warp of a launch hammers with atomics. It is kept apart from `best` and the plan:
    * loads of the first line used to queue behind the cursor atomics in the L2 (ncu: a third of the stall samples
    * of the LB1_d kernel sat on the load of `best`). ---- */

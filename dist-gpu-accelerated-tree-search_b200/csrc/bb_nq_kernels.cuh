@@ -830,24 +830,49 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
  */
 #define NQ5_TILES 8
 
+/*
+ * TAIL = 1 (the default engine, bb_config.packed = 3): nodes with at most `tail` columns left are not expanded level
+ * by level through the pool - the lane that read such a parent enumerates the whole subtree below it in registers,
+ * with an explicit stack of (rows used, diagonals, rows still to try) per level in the warp's shared memory, and only
+ * the counters leave the SM. The explored tree, the solutions, the parents decomposed and the candidates evaluated
+ * are counted node by node exactly as the level-by-level expansion counts them (a node with d queens placed is
+ * decomposed: parents + 1, candidates + N - d, tree + safe rows; with d = N - 1 its safe rows are solutions), so
+ * every total is the reference's. The `tail` deepest levels hold nearly all of the tree (N = 17: 99 % below depth
+ * 8), and they no longer cost 64 bytes of HBM traffic per node. The kernel argument G carries tail << 16.
+ */
+#define NQ5_WBUF_TILE1 1024                                   /* byte offsets in a warp's buffer */
+#define NQ5_WBUF_SURV 2048
+#define NQ5_WBUF_STAGE (NQ5_WBUF_SURV + BB_TILE_MAX * BB_MAX_QUEENS * 2)
+#define NQ5_WBUF_BYTES (NQ5_WBUF_STAGE + 32 * 48)
+#define NQ5_MAX_TAIL 9 /* stack levels: tail - 2 <= (NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 512 */
+
+template <int TAIL>
 __global__ void __launch_bounds__(BB_CTA_THREADS, 4)
-nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G)
+nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const int G_and_tail)
 {
   pdl_wait_then_release(); /* the plan and the pool are the previous iteration's output */
   const int nbatch = ctrl->n;
   if (nbatch == 0)
     return;
+  const int G = TAIL ? (G_and_tail & 0xffff) : G_and_tail;
+  const int cut = TAIL ? N - (G_and_tail >> 16) : N; /* parents at depth >= cut are enumerated to the end in place */
   const int cap = pool.capacity;
   const int src = ctrl->src, dst = 1 - src, base = ctrl->base;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t full = (N >= 32) ? 0xffffffffu : ((1u << N) - 1u);
 
   __shared__ uint32_t free_all[BB_WARPS_PER_CTA][NQ5_TILES * 32]; /* written and read by the same lane */
-  __shared__ uint4 tile_all[BB_WARPS_PER_CTA][2][2 * 32];
-  __shared__ uint16_t surv_all[BB_WARPS_PER_CTA][BB_TILE_MAX * BB_MAX_QUEENS];
-  __shared__ __align__(16) unsigned char stage_all[BB_WARPS_PER_CTA][32 * 48];
+  /* per warp: two tile buffers (2 planes x 32 parents), the tile's child list, one staging slot per lane; from the
+   * second tile buffer on it doubles as the lanes' DFS stacks [level][4 words][lane] while a round's parents are read */
+  __shared__ __align__(16) unsigned char wbuf_all[BB_WARPS_PER_CTA][NQ5_WBUF_BYTES];
+  static_assert((NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 512 >= NQ5_MAX_TAIL - 2, "DFS stack levels");
+  uint4(*tile_w)[2 * 32] = reinterpret_cast<uint4(*)[2 * 32]>(wbuf_all[warp]);
   uint32_t *free_s = free_all[warp];
-  uint16_t *surv_s = surv_all[warp];
+  uint16_t *surv_s = reinterpret_cast<uint16_t *>(wbuf_all[warp] + NQ5_WBUF_SURV);
+  unsigned char *stage_w = wbuf_all[warp] + NQ5_WBUF_STAGE;
+  uint32_t *stk = reinterpret_cast<uint32_t *>(wbuf_all[warp] + NQ5_WBUF_TILE1);
+  __shared__ unsigned long long dq_all[BB_WARPS_PER_CTA]; /* pass A: the warp's chunk of the batch */
+  __shared__ int dlock_all[BB_WARPS_PER_CTA];
 
   const uint4 *__restrict__ splanes = pool.planes[src];
   uint4 *__restrict__ dplanes = pool.planes[dst];
@@ -860,6 +885,122 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
   {
     const int nb = min(4, max(0, N - 4 * wi));
     vmask[wi] = nb == 4 ? 0x80808080u : (0x80808080u & ((1u << (8 * nb)) - 1u));
+  }
+
+  if (TAIL)
+  {
+    /* ---- pass A: the deep parents of the whole batch. Whichever LANE is free takes the next parent from its
+     * warp's chunk (a 64-bit word in shared memory: chunk base << 32 | next index, one atomicAdd hands out a parent
+     * and names its chunk consistently); a lane that finds the chunk used up refills it from the batch-wide counter.
+     * Subtree sizes differ by orders of magnitude: with fixed shares, or with a warp that waits at the end of every
+     * round, most lanes wait for the unluckiest one. ---- */
+    constexpr unsigned CH = 64;
+    if (lane == 0)
+    {
+      dq_all[warp] = (unsigned long long)(unsigned)nbatch << 32; /* an empty chunk */
+      dlock_all[warp] = 0;
+    }
+    __syncwarp();
+    int lvl = 0, d = 0;
+    uint32_t used = 0u, up = 0u, down = 0u, fr = 0u;
+    bool active = false;
+    for (;;)
+    {
+      if (!active)
+      {
+        const unsigned long long tk = atomicAdd(&dq_all[warp], 1ull);
+        const unsigned cb = (unsigned)(tk >> 32), ci = (unsigned)tk;
+        if (cb == 0xffffffffu)
+          break; /* the batch is handed out */
+        const unsigned ccnt = cb < (unsigned)nbatch ? min(CH, (unsigned)nbatch - cb) : 0u;
+        if (ci >= ccnt)
+        {
+          if (atomicCAS(&dlock_all[warp], 0, 1) == 0)
+          {
+            const unsigned long long now = *reinterpret_cast<volatile unsigned long long *>(&dq_all[warp]);
+            if ((unsigned)(now >> 32) == cb) /* nobody refilled it meanwhile */
+            {
+              const unsigned nb = atomicAdd(&ctrl->next_deep, CH);
+              atomicExch(&dq_all[warp], (unsigned long long)(nb < (unsigned)nbatch ? nb : 0xffffffffu) << 32);
+            }
+            __threadfence_block();
+            atomicExch(&dlock_all[warp], 0);
+          }
+          continue;
+        }
+        const uint4 pq = __ldg(splanes + (size_t)cap + base + cb + ci);
+        d = (int)(pq.y >> 24);
+        if (d < cut)
+          continue; /* a shallow parent: its children go to the pool in pass B */
+        used = pq.y & 0x00ffffffu;
+        up = pq.z;
+        down = pq.w;
+        /* the parent itself is decomposed here (nqueens_c.c:99-117) */
+        for (int g = 0; g < G; g++)
+        {
+          asm volatile("" : "+r"(used));
+          fr = ~(used | up | down) & full;
+        }
+        const int kids = __popc(fr);
+        apar++;
+        acand += N - d;
+        akids += kids;
+        if (d + 1 == N)
+        {
+          asol += kids;
+          fr = 0u;
+        }
+        lvl = 0;
+        active = fr != 0u;
+        continue;
+      }
+      if (fr == 0u)
+      {
+        if (lvl == 0)
+        {
+          active = false;
+          continue;
+        }
+        lvl--;
+        d--;
+        used = stk[(lvl * 4 + 0) * 32 + lane];
+        up = stk[(lvl * 4 + 1) * 32 + lane];
+        down = stk[(lvl * 4 + 2) * 32 + lane];
+        fr = stk[(lvl * 4 + 3) * 32 + lane];
+        continue;
+      }
+      /* place the lowest safe row: the child with d + 1 queens is decomposed at once */
+      const uint32_t bit = fr & (0u - fr);
+      fr ^= bit;
+      uint32_t nu = used | bit;
+      const uint32_t nup = ((up | bit) << 1) & full, ndn = (down | bit) >> 1;
+      uint32_t cfr = 0u;
+      for (int g = 0; g < G; g++)
+      {
+        asm volatile("" : "+r"(nu));
+        cfr = ~(nu | nup | ndn) & full;
+      }
+      const int ckids = __popc(cfr);
+      apar++;
+      acand += N - (d + 1);
+      akids += ckids;
+      if (d + 2 == N)
+        asol += ckids; /* its safe rows complete the board */
+      else if (cfr)
+      {
+        stk[(lvl * 4 + 0) * 32 + lane] = used;
+        stk[(lvl * 4 + 1) * 32 + lane] = up;
+        stk[(lvl * 4 + 2) * 32 + lane] = down;
+        stk[(lvl * 4 + 3) * 32 + lane] = fr;
+        lvl++;
+        d++;
+        used = nu;
+        up = nup;
+        down = ndn;
+        fr = cfr;
+      }
+    }
+    __syncwarp();
   }
 
   /* rounds are handed out through a counter, and get smaller towards the end of the batch (each warp asks for
@@ -900,7 +1041,7 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
-    fetch_tile(0, tile_all[warp][0]);
+    fetch_tile(0, tile_w[0]);
     /* ---- the round's free masks and child total ---- */
     int total = 0;
     {
@@ -919,7 +1060,7 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
         if (j * 32 >= rcnt) /* warp-uniform */
           break;
         const int depth = (int)(q[j].y >> 24);
-        const bool valid = depth != 255;
+        const bool valid = depth != 255 && !(TAIL && depth >= cut); /* deep parents were counted above */
         uint32_t used = q[j].y & 0x00ffffffu;
         const bool leaf = (depth + 1 == N);
         uint32_t fr = 0u;
@@ -962,8 +1103,8 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
     int buf = 0, off = 0;
     for (int t = 0; t < rtiles; t++)
     {
-      const uint4 *tile_s = tile_all[warp][buf];
-      fetch_tile(t + 1, tile_all[warp][buf ^ 1]);
+      const uint4 *tile_s = tile_w[buf];
+      fetch_tile(t + 1, tile_w[buf ^ 1]);
       buf ^= 1;
       asm volatile("cp.async.wait_group 1;" ::: "memory");
       __syncwarp();
@@ -1004,7 +1145,7 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
           const uint32_t used2 = ((q1.y & 0x00ffffffu) | bit) | ((uint32_t)(depth + 1) << 24);
           const uint32_t up2 = ((q1.z | bit) << 1) & full;
           const uint32_t down2 = (q1.w | bit) >> 1;
-          unsigned char *st = stage_all[warp] + lane * 48;
+          unsigned char *st = stage_w + lane * 48;
           *reinterpret_cast<uint4 *>(st) = q0;
           *reinterpret_cast<uint4 *>(st + 16) = make_uint4(q1.x, used2, up2, down2);
           const unsigned char bd = st[depth];

@@ -173,6 +173,7 @@ __device__ inline void plan_next(bb_ctrl *c, int preferred, int total_warps)
   c->ticket = 0;
   c->next_tile = 0;
   c->next_round = 0;
+  c->next_deep = 0;
 }
 
 /* programmatic dependent launch (bb_engine.cu launches the chained iterations with

@@ -172,8 +172,12 @@ typedef struct bb_config
   int lb2_stage_a;        /* LB2 staged kernel: pairs tried before the survivors are compacted; <=0: 8 */
   int lb2_table;          /* LB2 only: 1 = evaluate LB2 through the per-instance subset table (default; 2^n rows,
                              42 MB at 20x20, built on the device at engine creation), 0 = walk the machine pairs */
-  int packed;             /* 1 = second-generation kernels (default): PFSP two sibling children per lane in packed
-                             16-bit halves, N-Queens safe-row masks; 0 = first-generation, one child per lane */
+  int packed;             /* kernel generation. 3 (default): PFSP one lane per parent, two children per step in packed
+                             16-bit halves; N-Queens attack masks in the record, the last levels of the tree enumerated
+                             in registers by the lane that read the parent. 2: the same kernels, every N-Queens node
+                             through the pool (one iteration = one level of the popped parents). 1: second generation
+                             (two sibling children per lane on the warp tile; N-Queens safe-row masks rebuilt from the
+                             board). 0: first generation, one child per lane. All walk the same tree. */
 } bb_config;
 
 typedef struct bb_stats

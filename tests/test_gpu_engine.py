@@ -266,7 +266,7 @@ def test_nqueens_one_iteration_matches_oracle(N):
     kids = np.zeros((len(nodes) * N, orc.NQ_REC), np.uint8)
     k = L.orc_nq_generate_children(N, nodes, len(nodes), labels, C.byref(tree), C.byref(sol), kids)
     inner = kids[:k][kids[:k, 0] < N]
-    eng = bb.Engine.nqueens(N, 1)
+    eng = bb.Engine.nqueens(N, 1, packed=2)  # every node through the pool: one iteration = one level
     eng.reset()
     eng.push_nodes(nodes)
     assert node_set(eng.export_nodes(), 1 + N) == node_set(nodes, 1 + N)
@@ -274,6 +274,61 @@ def test_nqueens_one_iteration_matches_oracle(N):
     # depth-N children are counted (tree and sol) but not stored
     assert st.tree == tree.value and st.sol == k - len(inner) and st.pool_size == len(inner)
     assert node_set(eng.export_nodes(), 1 + N) == node_set(inner, 1 + N)
+    eng.close()
+
+
+@pytest.mark.parametrize("N,G", [(4, 1), (8, 1), (11, 3), (12, 1), (14, 1), (17, 1), (20, 1)])
+def test_nqueens_one_iteration_with_the_last_levels_in_registers(N, G):
+    """the default engine (bb_config.packed = 3): parents with at most 8 columns left are enumerated to the end by
+    the lane that read them, the others produce their children. After ONE iteration over random parents of every depth
+    the pool must hold exactly the checker's children of the shallow parents, and the counters must be the checker's
+    for one level of the shallow parents plus the whole subtrees of the deep ones (walked level by level here)."""
+    L = orc.oracle()
+    rng = np.random.default_rng(100 + N)
+    tail = 8
+    # deep parents: consistent boards (random placements of d non-attacking queens are rare, so walk down from the root)
+    level = np.zeros((1, orc.NQ_REC), np.uint8)
+    level[0, 1:1 + N] = np.arange(N)
+    picked = [level]
+    for d in range(N - 1):
+        labels = np.zeros(len(level) * N, np.uint8)
+        L.orc_nq_labels(N, 1, level, len(level), labels)
+        t, s_ = C.c_ulonglong(0), C.c_ulonglong(0)
+        kids = np.zeros((len(level) * N, orc.NQ_REC), np.uint8)
+        k = L.orc_nq_generate_children(N, level, len(level), labels, C.byref(t), C.byref(s_), kids)
+        kids = kids[:k][kids[:k, 0] < N]
+        if len(kids) == 0:
+            break
+        level = kids[rng.permutation(len(kids))[:60]]
+        picked.append(level[:25])
+    nodes = np.concatenate(picked + [orc.random_nq_nodes(rng, N, 300, 0, max(N - 1, 0))])
+    deep = nodes[:, 0] >= N - tail
+    shallow = nodes[~deep]
+
+    def one_level(par):
+        labels = np.zeros(max(len(par), 1) * N, np.uint8)
+        L.orc_nq_labels(N, G, par, len(par), labels)
+        t, s_ = C.c_ulonglong(0), C.c_ulonglong(0)
+        kids = np.zeros((max(len(par), 1) * N, orc.NQ_REC), np.uint8)
+        k = L.orc_nq_generate_children(N, par, len(par), labels, C.byref(t), C.byref(s_), kids)
+        kids = kids[:k]
+        return kids[kids[:, 0] < N], t.value, int((kids[:, 0] == N).sum())
+
+    exp_kids, tree, sol = one_level(shallow) if len(shallow) else (nodes[:0], 0, 0)
+    parents = len(shallow)
+    lvl = nodes[deep]
+    while len(lvl):
+        parents += len(lvl)
+        lvl, t, s_ = one_level(lvl)
+        tree, sol = tree + t, sol + s_
+    eng = bb.Engine.nqueens(N, G)
+    eng.reset()
+    eng.push_nodes(nodes)
+    st = eng.run(1)
+    assert (st.tree, st.sol, st.parents) == (tree, sol, parents)
+    assert st.pool_size == len(exp_kids)
+    if len(exp_kids):
+        assert node_set(eng.export_nodes(), 1 + N) == node_set(exp_kids, 1 + N)
     eng.close()
 
 

@@ -40,3 +40,10 @@ def test_earlier_kernel_generations_agree(packed):
     assert (res.tree, res.sol) == (4674889, 73712)
     res, _ = bb.nq_search(17 if packed else 16, 1, M=1 << 20, packed=packed)
     assert (res.tree, res.sol) == ((8017021931, 95815104) if packed else (1141190302, 14772512))
+
+
+def test_every_nqueens_node_through_the_pool_agrees():
+    """bb_config.packed = 2: the kernel of the default engine without the in-register enumeration of the last levels"""
+    for N, exp in ((13, (4674889, 73712)), (16, (1141190302, 14772512))):
+        res, per = bb.nq_search(N, 1, M=1 << 20, packed=2)
+        assert (res.tree, res.sol) == exp and per[0].parents == res.tree - res.sol + 1
