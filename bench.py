@@ -238,6 +238,12 @@ def roofline_objects(bb, w, ins, rec_pool, parents, nodes, evals, lb2_evals, ker
             "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1),
             "ncu_limiter": tr.get("limiter") if tr else None}
     extra = {}
+    if w[0] == "nq":
+        roof["note"] = ("the default engine enumerates the last min(9, N-7) levels of the tree in registers (the lane that "
+                        "read a parent walks the subtree below it; only the counters leave the SM), so most explored nodes "
+                        "are never written to or read from HBM and the SURVEY 8(d) byte count per node overstates the "
+                        "traffic: frac can exceed 1. The binding resource is then the instruction issue rate (ncu_limiter); "
+                        "bb_config.packed = 2 sends every node through the pool (0.43 of the HBM peak at N = 17).")
     if w[0] == "pfsp" and w[2] == 2:
         pk = C.c_double(0)
         bb.check(bb.lib.bb_measure_slot_step_peak(device, C.byref(pk)), "bb_measure_slot_step_peak")

@@ -1004,9 +1004,11 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
     /* packed = 2: every node goes through the pool (one launch = one level of every popped parent); packed = 3 (the
      * default): the last levels are enumerated in registers. BB_NQ_TAIL overrides the number of levels (tuning aid). */
     e->nq_tail = 0;
-    if (c_nq4 && c_nq5 && cfg && (cfg->packed >= 3 || cfg->packed < 0))
+    if (c_nq4 && c_nq5 && (!cfg || cfg->packed >= 3 || cfg->packed < 0))
     {
-      e->nq_tail = 8;
+      /* measured best on B200 (scripts/gpu_nq_tail_n.sh): 7 / 8 / 9 levels at N = 14 / 15 / 16+; deeper subtrees
+       * leave too few of them to keep every lane busy, shallower ones send more nodes through the pool */
+      e->nq_tail = N - 7;
       if (const char *t = getenv("BB_NQ_TAIL"))
         e->nq_tail = atoi(t);
       if (e->nq_tail > NQ5_MAX_TAIL)
@@ -1014,8 +1016,6 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
       if (e->nq_tail < 0)
         e->nq_tail = 0;
     }
-    if (!cfg && c_nq4 && c_nq5)
-      e->nq_tail = 8;
     if (G > 0xffff)
       e->nq_tail = 0; /* the kernel argument has 16 bits for G next to the tail */
     rc = setup_launch(e,
