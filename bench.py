@@ -231,7 +231,7 @@ def roofline_objects(bb, w, ins, rec_pool, parents, nodes, evals, lb2_evals, ker
     roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": tr["dram_bytes_per_launch"] if tr else None,
             "traffic_note": tr["note"] if tr else None, "peak_source": peak_src,
-            "kernel": {"nq_expand": "bbk::nq_expand5", "pfsp_expand_lb2": "bbk::pfsp_expand3<3,m>"}.get(
+            "kernel": {"nq_expand": "bbk::nq_expand5<1>", "pfsp_expand_lb2": "bbk::pfsp_expand3<3,m>"}.get(
                 kernel_key(w), "bbk::pfsp_expand3<lb,m>"),
             "algorithmic_bytes_per_node": 2 * rec_alg, "record_bytes_in_pool": rec_pool,
             "frac_pool_record": pool_bytes / (kernel_ms / 1e3) / 1e9 / peak,

@@ -3,7 +3,7 @@
 set -u
 tag=${1:-a}
 mkdir -p gpurun_out/r2
-for spec in "pfsp 21 2 8388608:200" "nq 17 8388608:450" "pfsp 22 0 4194304:80"; do
+for spec in "pfsp 21 2 8388608:200" "nq 17 8388608:8" "pfsp 22 0 4194304:80"; do
   args=${spec%%:*}; skip=${spec##*:}
   name=$(echo $args | cut -d' ' -f1-3 | tr ' ' '_')
   python scripts/profile_run.py $args > gpurun_out/r2/plain_${name}.log 2>&1 &&

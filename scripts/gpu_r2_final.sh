@@ -23,7 +23,7 @@ PY
 done
 timeout 300 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $out/prof_bench_plain.json 2> $out/prof_bench_plain.err &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $out/launches_bench.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline > $out/prof_bench_ncu.log 2>&1
-for spec in "pfsp 21 2 8388608:200" "nq 17 8388608:450" "pfsp 22 0 4194304:80"; do
+for spec in "pfsp 21 2 8388608:200" "nq 17 8388608:8" "pfsp 22 0 4194304:80"; do
   args=${spec%%:*}; skip=${spec##*:}
   name=$(echo $args | tr ' ' '_')
   timeout 200 python scripts/profile_run.py $args > $out/plain_${name}.log 2>&1 &&
