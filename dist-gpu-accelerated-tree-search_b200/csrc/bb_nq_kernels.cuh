@@ -961,9 +961,10 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
           active = false;
           continue;
         }
-        lvl--;
-        d--;
-        used = stk[(lvl * 4 + 0) * 32 + lane];
+        lvl--; /* the nearest ancestor that still has rows to try: frames without any are never pushed */
+        const uint32_t ud = stk[(lvl * 4 + 0) * 32 + lane];
+        used = ud & 0x00ffffffu;
+        d = (int)(ud >> 24);
         up = stk[(lvl * 4 + 1) * 32 + lane];
         down = stk[(lvl * 4 + 2) * 32 + lane];
         fr = stk[(lvl * 4 + 3) * 32 + lane];
@@ -981,18 +982,20 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
         cfr = ~(nu | nup | ndn) & full;
       }
       const int ckids = __popc(cfr);
-      apar++;
       acand += N - (d + 1);
       akids += ckids;
       if (d + 2 == N)
         asol += ckids; /* its safe rows complete the board */
       else if (cfr)
       {
-        stk[(lvl * 4 + 0) * 32 + lane] = used;
-        stk[(lvl * 4 + 1) * 32 + lane] = up;
-        stk[(lvl * 4 + 2) * 32 + lane] = down;
-        stk[(lvl * 4 + 3) * 32 + lane] = fr;
-        lvl++;
+        if (fr) /* nothing to come back to otherwise */
+        {
+          stk[(lvl * 4 + 0) * 32 + lane] = used | ((uint32_t)d << 24);
+          stk[(lvl * 4 + 1) * 32 + lane] = up;
+          stk[(lvl * 4 + 2) * 32 + lane] = down;
+          stk[(lvl * 4 + 3) * 32 + lane] = fr;
+          lvl++;
+        }
         d++;
         used = nu;
         up = nup;
@@ -1000,6 +1003,8 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
         fr = cfr;
       }
     }
+    /* every node below a deep parent that is not a solution was decomposed: parents = roots + (tree - solutions) */
+    apar += akids - asol;
     __syncwarp();
   }
 
