@@ -239,7 +239,7 @@ def roofline_objects(bb, w, ins, rec_pool, parents, nodes, evals, lb2_evals, ker
             "ncu_limiter": tr.get("limiter") if tr else None}
     extra = {}
     if w[0] == "nq":
-        roof["note"] = ("the default engine enumerates the last min(9, N-7) levels of the tree in registers (the lane that "
+        roof["note"] = ("the default engine enumerates the last min(12, N-7) levels of the tree in registers (the lane that "
                         "read a parent walks the subtree below it; only the counters leave the SM), so most explored nodes "
                         "are never written to or read from HBM and the SURVEY 8(d) byte count per node overstates the "
                         "traffic: frac can exceed 1. The binding resource is then the instruction issue rate (ncu_limiter); "

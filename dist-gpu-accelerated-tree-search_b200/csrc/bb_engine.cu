@@ -1006,8 +1006,9 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
     e->nq_tail = 0;
     if (c_nq4 && c_nq5 && (!cfg || cfg->packed >= 3 || cfg->packed < 0))
     {
-      /* measured best on B200 (scripts/gpu_nq_tail_n.sh): 7 / 8 / 9 levels at N = 14 / 15 / 16+; deeper subtrees
-       * leave too few of them to keep every lane busy, shallower ones send more nodes through the pool */
+      /* measured best on B200 (scripts/gpu_nq_tail_n.sh, gpu_nq_tail.sh): 7 / 8 / 9 / 10 / 11 levels at N = 14 / 15 /
+       * 16 / 17 / 18; deeper subtrees leave too few of them to keep every lane busy, shallower ones send more nodes
+       * through the pool */
       e->nq_tail = N - 7;
       if (const char *t = getenv("BB_NQ_TAIL"))
         e->nq_tail = atoi(t);

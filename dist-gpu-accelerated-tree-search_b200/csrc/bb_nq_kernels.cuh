@@ -844,7 +844,7 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 #define NQ5_WBUF_SURV 2048
 #define NQ5_WBUF_STAGE (NQ5_WBUF_SURV + BB_TILE_MAX * BB_MAX_QUEENS * 2)
 #define NQ5_WBUF_BYTES (NQ5_WBUF_STAGE + 32 * 48)
-#define NQ5_MAX_TAIL 9 /* stack levels: tail - 2 <= (NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 512 */
+#define NQ5_MAX_TAIL 12 /* stack levels of 3 words x 32 lanes: tail - 2 <= (NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 384 */
 
 template <int TAIL>
 __global__ void __launch_bounds__(BB_CTA_THREADS, 4)
@@ -863,9 +863,10 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 
   __shared__ uint32_t free_all[BB_WARPS_PER_CTA][NQ5_TILES * 32]; /* written and read by the same lane */
   /* per warp: two tile buffers (2 planes x 32 parents), the tile's child list, one staging slot per lane; from the
-   * second tile buffer on it doubles as the lanes' DFS stacks [level][4 words][lane] while a round's parents are read */
+   * second tile buffer on it doubles as the lanes' DFS stacks [level][3 words][lane] during pass A */
   __shared__ __align__(16) unsigned char wbuf_all[BB_WARPS_PER_CTA][NQ5_WBUF_BYTES];
-  static_assert((NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 512 >= NQ5_MAX_TAIL - 2, "DFS stack levels");
+  static_assert((NQ5_WBUF_BYTES - NQ5_WBUF_TILE1) / 384 >= NQ5_MAX_TAIL - 2, "DFS stack levels");
+  static_assert(BB_MAX_QUEENS <= 20, "stack frames pack 20-bit masks");
   uint4(*tile_w)[2 * 32] = reinterpret_cast<uint4(*)[2 * 32]>(wbuf_all[warp]);
   uint32_t *free_s = free_all[warp];
   uint16_t *surv_s = reinterpret_cast<uint16_t *>(wbuf_all[warp] + NQ5_WBUF_SURV);
@@ -962,12 +963,13 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
           continue;
         }
         lvl--; /* the nearest ancestor that still has rows to try: frames without any are never pushed */
-        const uint32_t ud = stk[(lvl * 4 + 0) * 32 + lane];
-        used = ud & 0x00ffffffu;
-        d = (int)(ud >> 24);
-        up = stk[(lvl * 4 + 1) * 32 + lane];
-        down = stk[(lvl * 4 + 2) * 32 + lane];
-        fr = stk[(lvl * 4 + 3) * 32 + lane];
+        /* a frame is three words: the four 20-bit masks packed, the depth is the number of rows used */
+        const uint32_t w0 = stk[(lvl * 3 + 0) * 32 + lane], w1 = stk[(lvl * 3 + 1) * 32 + lane];
+        down = stk[(lvl * 3 + 2) * 32 + lane];
+        used = w0 & 0xfffffu;
+        up = w1 & 0xfffffu;
+        fr = (w0 >> 20) | ((w1 >> 20) << 12);
+        d = __popc(used);
         continue;
       }
       /* place the lowest safe row: the child with d + 1 queens is decomposed at once */
@@ -990,10 +992,9 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
       {
         if (fr) /* nothing to come back to otherwise */
         {
-          stk[(lvl * 4 + 0) * 32 + lane] = used | ((uint32_t)d << 24);
-          stk[(lvl * 4 + 1) * 32 + lane] = up;
-          stk[(lvl * 4 + 2) * 32 + lane] = down;
-          stk[(lvl * 4 + 3) * 32 + lane] = fr;
+          stk[(lvl * 3 + 0) * 32 + lane] = used | (fr << 20);
+          stk[(lvl * 3 + 1) * 32 + lane] = up | ((fr >> 12) << 20);
+          stk[(lvl * 3 + 2) * 32 + lane] = down;
           lvl++;
         }
         d++;

@@ -279,13 +279,13 @@ def test_nqueens_one_iteration_matches_oracle(N):
 
 @pytest.mark.parametrize("N,G", [(4, 1), (8, 1), (11, 3), (12, 1), (14, 1), (17, 1), (20, 1)])
 def test_nqueens_one_iteration_with_the_last_levels_in_registers(N, G):
-    """the default engine (bb_config.packed = 3): parents with at most min(9, N - 7) columns left are enumerated to the end by
+    """the default engine (bb_config.packed = 3): parents with at most min(12, N - 7) columns left are enumerated to the end by
     the lane that read them, the others produce their children. After ONE iteration over random parents of every depth
     the pool must hold exactly the checker's children of the shallow parents, and the counters must be the checker's
     for one level of the shallow parents plus the whole subtrees of the deep ones (walked level by level here)."""
     L = orc.oracle()
     rng = np.random.default_rng(100 + N)
-    tail = min(9, max(0, N - 7))
+    tail = min(12, max(0, N - 7))
     # deep parents: consistent boards (random placements of d non-attacking queens are rare, so walk down from the root)
     level = np.zeros((1, orc.NQ_REC), np.uint8)
     level[0, 1:1 + N] = np.arange(N)
@@ -300,8 +300,13 @@ def test_nqueens_one_iteration_with_the_last_levels_in_registers(N, G):
         if len(kids) == 0:
             break
         level = kids[rng.permutation(len(kids))[:60]]
-        picked.append(level[:25])
-    nodes = np.concatenate(picked + [orc.random_nq_nodes(rng, N, 300, 0, max(N - 1, 0))])
+        if d + 1 < N - tail or d + 1 >= N - 6:  # shallow parents, and deep ones whose subtrees the checker can walk
+            picked.append(level[:25])
+        elif d + 1 == N - tail:
+            picked.append(level[:2])            # two whole subtrees of the full height
+    rnd = orc.random_nq_nodes(rng, N, 300, 0, max(N - 1, 0))
+    rnd = rnd[(rnd[:, 0] < N - tail) | (rnd[:, 0] >= N - 6)]
+    nodes = np.concatenate(picked + [rnd])
     deep = nodes[:, 0] >= N - tail
     shallow = nodes[~deep]
 
