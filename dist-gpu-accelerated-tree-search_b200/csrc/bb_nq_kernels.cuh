@@ -970,7 +970,9 @@ nq_expand5(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
         up = w1 & 0xfffffu;
         fr = (w0 >> 20) | ((w1 >> 20) << 12);
         d = __popc(used);
-        continue;
+        /* a pushed frame always has a row left, so the lane goes on to place it in this same pass of the loop: a
+         * pass that only backtracks would keep the lane out of the instructions below, which the rest of the warp
+         * executes anyway */
       }
       /* place the lowest safe row: the child with d + 1 queens is decomposed at once */
       const uint32_t bit = fr & (0u - fr);
