@@ -1010,6 +1010,8 @@ static int create_nq(bb_engine *e, int N, int G, const bb_config *cfg)
        * 16 / 17 / 18; deeper subtrees leave too few of them to keep every lane busy, shallower ones send more nodes
        * through the pool */
       e->nq_tail = N - 7;
+      if (cfg && cfg->packed >= 4)
+        e->nq_tail -= cfg->packed - 3; /* workers of a team of >= 4: each holds a share of the parents only */
       if (const char *t = getenv("BB_NQ_TAIL"))
         e->nq_tail = atoi(t);
       if (e->nq_tail > NQ5_MAX_TAIL)

@@ -192,7 +192,8 @@ int seed_partition(bb_engine *e, int kind, int D, int me, int m_keep, int best0,
   return bb_engine_partition(e, D, me, 1);
 }
 
-bb_engine *create_engine(int kind, const bb_pfsp_instance *ins, int lb, int N, int G, const bb_config *cfg, int device)
+bb_engine *create_engine(int kind, const bb_pfsp_instance *ins, int lb, int N, int G, const bb_config *cfg, int device,
+                         int team = 1)
 {
   bb_config c;
   if (cfg)
@@ -200,6 +201,11 @@ bb_engine *create_engine(int kind, const bb_pfsp_instance *ins, int lb, int N, i
   else
     bb_config_default(&c);
   c.device = device;
+  /* N-Queens, last levels in registers: a worker of a team of four or more holds so few deep parents that whole
+   * subtrees of the single-GPU height leave lanes idle at the end of a launch (8 GPUs, N = 17: 5 subtrees per lane);
+   * one level less gives eight times as many, smaller ones */
+  if (kind != KIND_PFSP && team >= 4 && c.packed == 3)
+    c.packed = 4;
   if (c.capacity <= 0)
   {
     /* a worker of a multi-GPU search holds only its share of the tree: 26 x M nodes per stack keep the planner's
@@ -335,7 +341,7 @@ int bb_multi_search(int kind, const bb_pfsp_instance *ins, int lb, int best0, in
         bb_team_fail(team);
       };
       const double c0 = now_s();
-      w.e = create_engine(kind, ins, lb, N, G, &c, dev_of(i));
+      w.e = create_engine(kind, ins, lb, N, G, &c, dev_of(i), D);
       if (!w.e)
         fail(BB_ERR_CUDA);
       else if (bb_engine_stage_alloc(w.e, BB_STAGE_BYTES) != BB_OK)
@@ -510,7 +516,7 @@ bb_dist *dist_open(int kind, const bb_pfsp_instance *ins, int lb, int N, int G, 
   if (!rc)
   {
     const double c0 = now_s();
-    d->e = create_engine(kind, ins, lb, N, G, &d->c, d->c.device);
+    d->e = create_engine(kind, ins, lb, N, G, &d->c, d->c.device, world);
     d->setup_s = now_s() - c0;
     if (!d->e)
       rc = BB_ERR_CUDA;
