@@ -832,13 +832,16 @@ nq_expand4(bb_ctrl *__restrict__ ctrl, const bb_pool pool, const int N, const in
 
 /*
  * TAIL = 1 (the default engine, bb_config.packed = 3): nodes with at most `tail` columns left are not expanded level
- * by level through the pool - the lane that read such a parent enumerates the whole subtree below it in registers,
- * with an explicit stack of (rows used, diagonals, rows still to try) per level in the warp's shared memory, and only
- * the counters leave the SM. The explored tree, the solutions, the parents decomposed and the candidates evaluated
- * are counted node by node exactly as the level-by-level expansion counts them (a node with d queens placed is
- * decomposed: parents + 1, candidates + N - d, tree + safe rows; with d = N - 1 its safe rows are solutions), so
- * every total is the reference's. The `tail` deepest levels hold nearly all of the tree (N = 17: 99 % below depth
- * 8), and they no longer cost 64 bytes of HBM traffic per node. The kernel argument G carries tail << 16.
+ * by level through the pool. In pass A of a launch whichever lane is free takes the next such parent of the batch and
+ * enumerates the whole subtree below it: the three masks of the current node in registers, an explicit stack in the
+ * warp's shared memory (one frame = three words: rows used, the two diagonal masks and the rows still to try as four
+ * packed 20-bit masks; the depth is the number of rows used; a node without rows left is never pushed). Only the
+ * counters leave the SM. The explored tree, the solutions, the parents decomposed and the candidates evaluated are
+ * what the level-by-level expansion counts (a node with d queens placed is decomposed: candidates + N - d, tree +
+ * safe rows; with d = N - 1 its safe rows are solutions; parents = deep parents + (tree - solutions) below them),
+ * so every total is the reference's. The deepest levels hold nearly all of the tree (N = 17: 99 % below depth 7)
+ * and no longer cost 64 bytes of HBM traffic per node. Pass B is the round loop for the other parents. The kernel
+ * argument G carries tail << 16.
  */
 #define NQ5_WBUF_TILE1 1024                                   /* byte offsets in a warp's buffer */
 #define NQ5_WBUF_SURV 2048
