@@ -238,6 +238,10 @@ def roofline_objects(bb, w, ins, rec_pool, parents, nodes, evals, lb2_evals, ker
             "algorithmic_bytes_per_launch": alg_bytes / max(iters, 1), "avg_launch_us": kernel_ms * 1e3 / max(iters, 1),
             "ncu_limiter": tr.get("limiter") if tr else None}
     extra = {}
+    if w[0] == "nq" and tr and tr.get("issue"):
+        # what binds the default N-Queens engine: the issue rate of the launch that enumerates the deep subtrees
+        # (static figure from the committed ncu capture of this kernel; see profiles/ncu_traffic.json)
+        extra["roofline_issue"] = tr["issue"]
     if w[0] == "nq":
         roof["note"] = ("the default engine enumerates the last min(12, N-7) levels of the tree in registers (the lane that "
                         "read a parent walks the subtree below it; only the counters leave the SM), so most explored nodes "
